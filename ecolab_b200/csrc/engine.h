@@ -1,0 +1,171 @@
+// engine.h -- internal interface between the host model (model.cpp, the C ABI)
+// and the device store + sm_100a kernels (engine.cu).  Not a public header; the
+// public boundary is include/ecolab_b200.h.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace eco {
+
+// One mutation event produced by the per-cell speciation kernel:
+// `count` mutants of parent species slot `slot` were born in cell `cell`.
+struct MutRecord {
+  uint32_t cell, slot, count;
+};
+
+// beta in "grouped ELL" form: species rows are processed four at a time (one
+// Philox4x32 call yields the four draws of a row group); each group has
+// width = max row length in the group, shorter rows padded with (val 0, col 0).
+// Term order inside a row is the COO order (reference oDiagIdx,
+// models/ecolab_model.cc:718-723) so the FP64 summation order is unchanged.
+struct BetaGell {
+  uint32_t nsp = 0, ngroups = 0;
+  std::vector<uint32_t> gptr;   // [ngroups+1] slot offsets
+  std::vector<double> gval;     // [nslots*4]
+  std::vector<uint32_t> gcol;   // [nslots*4] column * 32 (word offset of the species row in a tile)
+  std::vector<double> diag4;    // [ngroups*4]
+  std::vector<double> rr4;      // [ngroups*4] repro_rate
+};
+
+class Engine {
+ public:
+  explicit Engine(int device);
+  ~Engine();
+
+  // ---- geometry / storage -------------------------------------------------
+  // This process owns grid rows [y0, y0+ny) of an nx x ny_global grid
+  // (single GPU: y0=0, ny=ny_global).  Density is reset to zero.
+  void set_grid(uint32_t nx, uint32_t ny_global, uint32_t y0, uint32_t ny, uint32_t nsp);
+  // Change the species count (keeps existing rows; new rows are zero).
+  void resize_species(uint32_t nsp);
+  uint32_t nsp() const { return nsp_; }
+  uint32_t nx() const { return nx_; }
+  uint32_t ny() const { return ny_; }
+  uint32_t y0() const { return y0_; }
+  uint32_t ny_global() const { return nyg_; }
+  size_t ncells_local() const { return (size_t)nx_ * ny_; }
+
+  void set_stream(void* s);
+  void* stream() const { return (void*)stream_; }
+  void sync();
+
+  // density access, cells addressed by LOCAL index x + nx*(y-y0)
+  void set_density(size_t cell, const int32_t* d, size_t n);
+  void get_density(size_t cell, int32_t* d, size_t n);
+  // all local cells, host buffer cell-major [cell][nsp]; goes through a pinned/
+  // device staging buffer and a transposing kernel
+  void set_density_all(const int32_t* host, size_t nsp);
+  void get_density_all(int32_t* host, size_t nsp);
+  // same with a DEVICE cell-major buffer (used by bench to build big states)
+  void set_density_all_dev(const int32_t* dev, size_t nsp);
+  void get_density_all_dev(int32_t* dev, size_t nsp);
+  void fill_density(int32_t v);
+
+  // ---- species data ---------------------------------------------------------
+  void upload_beta(const BetaGell& b);
+
+  // ---- hot path -------------------------------------------------------------
+  // niter fused Lotka-Volterra steps on every owned cell; t0 = absolute tstep of the first
+  void generate(uint32_t niter, uint64_t t0, uint32_t seed);
+  // cm[s] = capped migration coefficient; returns sum |delta| over owned cells (not halved)
+  uint64_t migrate(const double* cm_host, bool wait_result = true);
+  uint64_t migrate_result();   // blocks on the async total of the last migrate
+  // alive[s] = 1 iff some owned cell has density != 0
+  void alive_mask(uint8_t* alive_host);
+  // compact species rows: keep[s] != 0 survives, order preserved
+  void compact_species(const uint8_t* keep_host, uint32_t nkeep);
+  // speciation: k = ROUND(ms[s] * n), n -= k; returns records sorted by (cell, slot); cell ids GLOBAL
+  void mutate_cells(const double* ms_host, uint64_t t, uint32_t seed, std::vector<MutRecord>& out);
+  // append one species per (global) cell id in `cells`: density 1 in that cell if owned, else 0
+  void append_species(const uint32_t* cells, size_t m);
+  // number of non-zero densities per owned cell
+  void nsp_per_cell(uint32_t* out_host);
+  // per-species totals over owned cells
+  void species_totals(int64_t* out_host);
+
+  // ---- multi-GPU halo -------------------------------------------------------
+  // Device pointers of the boundary rows to send and the ghost rows to receive
+  // (each row_bytes() long, contiguous).  Valid until the next migrate()/resize.
+  void halo_ptrs(void** send_top, void** send_bottom, void** recv_top, void** recv_bottom);
+  size_t row_bytes() const { return (size_t)ntx_ * cap_ * 32 * sizeof(int32_t); }
+  // Optional peer pointers (CUDA IPC / P2P): when set, migrate reads the
+  // neighbour slabs' boundary rows directly over NVLink instead of ghost rows.
+  void set_peer_rows(const void* top_peer_row, const void* bottom_peer_row);
+  int ipc_export(void* handle_out64, size_t* offset_top, size_t* offset_bottom);
+  void* ipc_import(const void* handle64);
+
+  // x = n + n*(r+ir) before ROUND for one generate sub-step, cell-major [cell][nsp]; densities untouched
+  void pre_rounding(double* out_host);
+
+  // per-kernel device timing (CUDA events on the engine stream), off by default
+  enum KernelKind { K_GENERATE = 0, K_MIGRATE = 1, K_STEP = 2, K_COUNT = 3 };
+  bool timing = false;
+  void kernel_times(double* ms, uint64_t* count);   // arrays of K_COUNT; synchronises the stream
+  void reset_kernel_times();
+
+  // diagnostics
+  uint64_t launches() const { return launches_; }
+  void reset_launches() { launches_ = 0; }
+  size_t bytes_allocated() const;
+  int device() const { return device_; }
+  void last_kernel_config(int* grid, int* block, int* smem) const {
+    *grid = last_grid_; *block = last_block_; *smem = last_smem_;
+  }
+  // tuning knobs (bench/profiling): 0 = auto
+  int gen_variant = 0;
+  int mig_variant = 0;
+
+ private:
+  void ensure_other();
+  void alloc_buffers(uint32_t cap);
+  void free_buffers();
+  int32_t* row0(int which) const;   // pointer to owned row 0 of buffer `which`
+  size_t tile_stride() const { return (size_t)cap_ * 32; }
+  size_t row_stride() const { return (size_t)ntx_ * cap_ * 32; }
+
+  int device_ = 0;
+  void* stream_ = nullptr;
+  bool own_stream_ = false;
+  int num_sms_ = 148;
+  int max_smem_ = 0;
+
+  uint32_t nx_ = 1, nyg_ = 1, y0_ = 0, ny_ = 1, ntx_ = 1;
+  uint32_t nsp_ = 0, cap_ = 0;
+  int32_t* buf_[2] = {nullptr, nullptr};   // allocations (with ghost rows)
+  int cur_ = 0;
+  const void* peer_top_ = nullptr;
+  const void* peer_bottom_ = nullptr;
+
+  // beta on device
+  uint32_t ngroups_ = 0;
+  uint32_t* d_gptr_ = nullptr; double* d_gval_ = nullptr; uint32_t* d_gcol_ = nullptr;
+  double* d_diag4_ = nullptr; double* d_rr4_ = nullptr;
+  size_t beta_cap_slots_ = 0, beta_cap_groups_ = 0;
+  uint32_t max_width_ = 0;
+
+  // scratch
+  double* d_vec_ = nullptr; size_t vec_cap_ = 0;       // per-species doubles (cm / ms)
+  uint8_t* d_mask_ = nullptr; uint32_t* d_map_ = nullptr; size_t mask_cap_ = 0;
+  unsigned long long* d_total_ = nullptr;              // migrate total / counters
+  unsigned long long* h_total_ = nullptr;              // pinned
+  MutRecord* d_rec_ = nullptr; size_t rec_cap_ = 0;
+  int32_t* d_stage_ = nullptr; size_t stage_cap_ = 0;  // cell-major staging
+  void* ev_total_ = nullptr;
+
+  uint64_t launches_ = 0;
+  int last_grid_ = 0, last_block_ = 0, last_smem_ = 0;
+
+  struct PendingEvent { void* start; void* stop; int kind; };
+  std::vector<PendingEvent> ev_pending_;
+  std::vector<void*> ev_pool_;
+  double kt_ms_[K_COUNT] = {0, 0, 0};
+  uint64_t kt_n_[K_COUNT] = {0, 0, 0};
+  void time_begin(int kind);
+  void time_end();
+};
+
+void check_cuda(int err, const char* what, const char* file, int line);
+
+}  // namespace eco

@@ -1,0 +1,936 @@
+// model.cpp -- host side of the engine: the ModelData / PanmicticModel /
+// SpatialModel state machine of the reference (models/ecolab_model.{h,cc}) kept
+// in C++ above the CUDA device store, and the C ABI declared in
+// include/ecolab_b200.h.  Species-level bookkeeping (condense of the parameter
+// arrays, parameter mutation) is O(nsp + nnz) serial host work exactly as in the
+// reference; everything O(cells x species) runs in engine.cu on the GPU.
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/ecolab_b200.h"
+#include "engine.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+// ---- the reference's process-wide generators (src/arrays.cc:24-25) -----------------
+// array_urand: libc rand()/RAND_MAX (src/random.cc:57); array_grand: running-CLT
+// generator (src/random.cc:59-64).  Kept semantically identical so that
+// `array_urand.seed(n)` in the driver scripts means the same thing.
+inline double urand01() { return ((double)::rand()) / RAND_MAX; }
+struct RunningClt {
+  double sum = 0;
+  unsigned n = 0;
+  double next() {
+    sum += urand01();
+    ++n;
+    return (sum - .5 * n) * std::sqrt(12. / n);
+  }
+} g_grand;
+
+// host copy of the Philox4x32-10 stream (only for the `salt` getter)
+uint32_t philox_host(uint32_t seed, uint32_t stage, uint32_t cell, uint32_t slot, uint64_t t) {
+  uint32_t c0 = cell, c1 = slot >> 2, c2 = (uint32_t)t, c3 = (uint32_t)(t >> 32), k0 = seed, k1 = stage;
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  const uint32_t o[4] = {c0, c1, c2, c3};
+  return o[slot & 3];
+}
+
+void add_noise(std::vector<double>& a, const std::vector<double>& scale) {          // gspread, src/arrays.cc:94-100
+  std::vector<double> z(a.size());
+  for (double& v : z) v = g_grand.next();
+  for (size_t i = 0; i < a.size(); ++i) a[i] += scale[i] * z[i];
+}
+void mul_lognoise(std::vector<double>& a, const std::vector<double>& scale) {       // lgspread, src/arrays.cc:85-92
+  std::vector<double> z(a.size());
+  for (double& v : z) v = g_grand.next();
+  for (size_t i = 0; i < a.size(); ++i) {
+    const double sgn = a[i] >= 0 ? 1.0 : -1.0;
+    a[i] = sgn * std::exp(std::log(std::fabs(a[i])) + scale[i] * z[i]);
+  }
+}
+
+}  // namespace
+
+struct eco_model {
+  // ---- ModelData (models/ecolab_model.h:39-68) ----
+  std::vector<int32_t> species;
+  std::vector<double> create, repro_rate, mutation, migration, diag, val;
+  std::vector<uint32_t> row, col;
+  uint64_t tstep = 0, last_mut_tstep = 0, last_mig_tstep = 0;
+  double sp_sep = 0.1, mut_max = 0, repro_min = 0, repro_max = 1, odiag_min = 0, odiag_max = 1, gen_bias = 0;
+  bool fixMutation = false, fixMigration = false;
+  // ---- SpatialModel (models/ecolab_model.h:128-151) ----
+  bool panmictic = true;
+  size_t numX = 1, numY = 1, maxNbrs = 0;
+  size_t y0 = 0, nyl = 1;      // owned slab
+  unsigned nprocs = 1;
+  // ---- engine ----
+  eco::Engine eng;
+  bool beta_dirty = true;
+  uint32_t seed = 0;
+  uint64_t salt_t = 0;
+  int sp_cntr = -1;   // the reference's function-static species label counter (models/ecolab_model.cc:366)
+  std::vector<eco::MutRecord> pending;   // records of the last eco_mutate_cells
+
+  explicit eco_model(int dev) : eng(dev) { eng.set_grid(1, 1, 0, 1, 0); }
+
+  size_t nsp() const { return species.size(); }
+  size_t ncells_local() const { return numX * nyl; }
+
+  void grow_engine(size_t n) {
+    if (n > eng.nsp()) { eng.resize_species((uint32_t)n); }
+  }
+
+  // ModelData::makeConsistent :705-716 + SpatialModel::makeConsistent :725-735
+  void makeConsistent() {
+    size_t n = std::max(nsp(), (size_t)eng.nsp());
+    if (species.empty()) {
+      species.resize(n);
+      for (size_t i = 0; i < n; ++i) species[i] = (int32_t)i;
+    }
+    if (create.empty()) create.assign(nsp(), 0);
+    if (mutation.empty()) mutation.assign(nsp(), 0);
+    if (migration.empty()) migration.assign(nsp(), 0);
+    grow_engine(nsp());
+    beta_dirty = true;   // computeODiagIdx :718-723 happens in upload()
+  }
+
+  void check_sizes(bool need_migration) {
+    const size_t n = nsp();
+    auto bad = [&](const char* what, size_t have) {
+      char b[256];
+      snprintf(b, sizeof b, "inconsistent model: %s has %zu entries but there are %zu species", what, have, n);
+      throw std::runtime_error(b);
+    };
+    if (eng.nsp() > n) bad("cell density", eng.nsp());
+    grow_engine(n);
+    if (repro_rate.size() != n) bad("repro_rate", repro_rate.size());
+    if (diag.size() != n) bad("interaction.diag", diag.size());
+    if (need_migration && migration.size() != n) bad("migration", migration.size());
+    if (row.size() != val.size() || col.size() != val.size())
+      throw std::runtime_error("inconsistent model: interaction.row/col/val differ in length");
+  }
+
+  // build the grouped-ELL form of beta; term order inside a row = COO order (oDiagIdx, :718-723)
+  void upload() {
+    if (!beta_dirty) return;
+    const uint32_t n = (uint32_t)nsp();
+    std::vector<uint32_t> cnt(n + 1, 0);
+    for (size_t j = 0; j < row.size(); ++j) {
+      if (row[j] >= n || col[j] >= n) throw std::runtime_error("interaction.row/col index out of range");
+      ++cnt[row[j] + 1];
+    }
+    for (uint32_t i = 0; i < n; ++i) cnt[i + 1] += cnt[i];
+    std::vector<uint32_t> order(row.size()), pos(cnt.begin(), cnt.end() - 1);
+    for (size_t j = 0; j < row.size(); ++j) order[pos[row[j]]++] = (uint32_t)j;   // stable: ascending j inside a row
+    eco::BetaGell b;
+    b.nsp = n;
+    b.ngroups = (n + 3) / 4;
+    b.gptr.assign(b.ngroups + 1, 0);
+    for (uint32_t g = 0; g < b.ngroups; ++g) {
+      uint32_t w = 0;
+      for (uint32_t r = 0; r < 4 && 4 * g + r < n; ++r) w = std::max(w, cnt[4 * g + r + 1] - cnt[4 * g + r]);
+      b.gptr[g + 1] = b.gptr[g] + w;
+    }
+    const size_t nslots = b.gptr[b.ngroups];
+    b.gval.assign(nslots * 4, 0.0);
+    b.gcol.assign(nslots * 4, 0u);
+    b.diag4.assign((size_t)b.ngroups * 4, 0.0);
+    b.rr4.assign((size_t)b.ngroups * 4, 0.0);
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint32_t g = i / 4, r = i % 4;
+      b.diag4[i] = diag[i];
+      b.rr4[i] = repro_rate[i];
+      for (uint32_t k = cnt[i]; k < cnt[i + 1]; ++k) {
+        const size_t slot = (size_t)b.gptr[g] + (k - cnt[i]);
+        b.gval[slot * 4 + r] = val[order[k]];
+        b.gcol[slot * 4 + r] = col[order[k]] * 32u;
+      }
+    }
+    eng.upload_beta(b);
+    beta_dirty = false;
+  }
+
+  // SpatialModel::setGrid :580-605
+  void setGrid(size_t nx, size_t ny, size_t y0_, size_t nyl_) {
+    if (!nx || !ny) throw std::runtime_error("setGrid: empty grid");
+    if (nx * ny > 0xffffffffull) throw std::runtime_error("setGrid: more than 2^32 cells");
+    if (y0_ + nyl_ > ny) throw std::runtime_error("setGrid: slab outside the grid");
+    panmictic = false;
+    numX = nx; numY = ny; y0 = y0_; nyl = nyl_;
+    eng.set_grid((uint32_t)nx, (uint32_t)ny, (uint32_t)y0, (uint32_t)nyl, (uint32_t)nsp());
+    const size_t nb = std::min<size_t>(nx - 1, 2) + std::min<size_t>(ny - 1, 2);
+    maxNbrs = std::max(maxNbrs, nb);   // never shrinks (:603-604)
+  }
+
+  size_t local_cell(size_t cell) const {
+    if (cell >= numX * numY) throw std::runtime_error("cell id outside the grid");
+    const size_t y = cell / numX;
+    if (y < y0 || y >= y0 + nyl) throw std::runtime_error("cell is not owned by this process");
+    return cell - y0 * numX;
+  }
+
+  void generate(unsigned niter) {
+    if (tstep == 0) makeConsistent();
+    check_sizes(false);
+    upload();
+    eng.generate(niter, tstep, seed);
+    tstep += niter;
+  }
+
+  uint64_t migrate_local() {
+    check_sizes(true);
+    const size_t n = nsp();
+    std::vector<double> cm(n);
+    const double cap = 1.0 / maxNbrs;   // :628
+    for (size_t s = 0; s < n; ++s) {
+      const double mm = (tstep - last_mig_tstep) * migration[s];   // :626
+      cm[s] = mm > cap ? cap : mm;                                  // :629
+    }
+    salt_t = tstep;
+    const uint64_t total = n ? eng.migrate(cm.data()) : 0;
+    last_mig_tstep = tstep;
+    return total;
+  }
+
+  // ModelData::condense :139-159
+  void condenseModel(const std::vector<uint8_t>& mask) {
+    const size_t n = nsp();
+    std::vector<uint32_t> map(n);
+    uint32_t k = 0;
+    for (size_t i = 0; i < n; ++i) { map[i] = k; k += mask[i] ? 1 : 0; }
+    auto squeeze = [&](auto& a) {
+      size_t w = 0;
+      for (size_t i = 0; i < a.size() && i < n; ++i) if (mask[i]) a[w++] = a[i];
+      a.resize(w);
+    };
+    squeeze(create); squeeze(species); squeeze(repro_rate); squeeze(mutation); squeeze(migration); squeeze(diag);
+    size_t w = 0;
+    for (size_t j = 0; j < val.size(); ++j)
+      if (mask[row[j]] && mask[col[j]]) { val[w] = val[j]; row[w] = map[row[j]]; col[w] = map[col[j]]; ++w; }
+    val.resize(w); row.resize(w); col.resize(w);
+    beta_dirty = true;
+  }
+
+  unsigned condense_apply(const std::vector<uint8_t>& mask) {
+    const size_t n = nsp();
+    size_t ntrue = 0;
+    for (uint8_t b : mask) ntrue += b ? 1 : 0;
+    if (ntrue == n) return 0;
+    condenseModel(mask);
+    eng.compact_species(mask.data(), (uint32_t)ntrue);
+    return (unsigned)(n - ntrue);
+  }
+
+  unsigned condense() {
+    if (panmictic && species.empty()) makeConsistent();
+    const size_t n = nsp();
+    if (eng.nsp() != n) check_sizes(false);
+    std::vector<uint8_t> mask(n, 0);
+    if (n) eng.alive_mask(mask.data());
+    return condense_apply(mask);
+  }
+
+  // do_row_or_col, models/ecolab_model.cc:327-359
+  void perturb_links(std::vector<double>& t, double range, double minval, double gd) {
+    double r = (2.0 * ::rand()) / RAND_MAX - 1 + gen_bias;
+    r = r > 0 ? r / (1 + gen_bias) : r / (1 - gen_bias);
+    size_t cnt = t.size();
+    if (r != 0) {
+      const double inv = 1 / std::fabs(r);
+      if (inv < 2147483648.0) cnt = (size_t)(unsigned)((int)inv - 1);
+    }
+    cnt = std::min(cnt, t.size());
+    const double span = (double)(t.size() - 1);
+    for (size_t j = 0; j < cnt; ++j) {
+      const int pos = (int)(span * ((double)::rand() / RAND_MAX) + .5);
+      if (r > 0) {
+        if (t[pos] == 0.0) t[pos] = range * ((double)::rand() / RAND_MAX) + minval;
+      } else
+        t[pos] = 0;
+    }
+    std::vector<double> sc(t.size());
+    for (size_t i = 0; i < t.size(); ++i) sc[i] = t[i] != 0.0 ? range * gd : 0.0;
+    add_noise(t, sc);
+  }
+
+  // ModelData::mutate :362-470 -- one new species per entry of `parents`
+  void mutateModel(const std::vector<uint32_t>& parents) {
+    const size_t m = parents.size();
+    if (!m) return;
+    const size_t n0 = nsp();
+    for (uint32_t p : parents) if (p >= n0) throw std::runtime_error("mutate: parent slot out of range");
+    if (sp_cntr == -1) sp_cntr = *std::max_element(species.begin(), species.end()) + 1;
+
+    std::vector<double> gd(m);                                   // genetic distances (:371-373)
+    for (double& g : gd) g = -std::log(urand01());
+    for (size_t k = 0; k < m; ++k) gd[k] *= mutation[parents[k]];
+
+    std::vector<double> r_new(m), sc(m);
+    for (size_t k = 0; k < m; ++k) { r_new[k] = repro_rate[parents[k]]; sc[k] = (repro_max - repro_min) * gd[k]; }
+    add_noise(r_new, sc);                                        // :380-383
+    repro_rate.insert(repro_rate.end(), r_new.begin(), r_new.end());
+
+    std::vector<double> mu(m);
+    for (size_t k = 0; k < m; ++k) mu[k] = mutation[parents[k]];
+    if (!fixMutation) mul_lognoise(mu, gd);
+    for (size_t k = 0; k < m; ++k) mutation.push_back(mu[k] < mut_max ? mu[k] : mut_max);   // :389
+
+    std::vector<double> mg(m);
+    for (size_t k = 0; k < m; ++k) mg[k] = migration[parents[k]];
+    if (!fixMigration) mul_lognoise(mg, gd);
+    migration.insert(migration.end(), mg.begin(), mg.end());
+
+    std::vector<double> dg(m);
+    for (size_t k = 0; k < m; ++k) dg[k] = diag[parents[k]];
+    mul_lognoise(dg, gd);
+    for (size_t k = 0; k < m; ++k) {
+      const double lim = -std::fabs(r_new[k]) / (0.1 * INT_MAX);   // :402
+      diag.push_back(dg[k] < lim ? dg[k] : lim);
+    }
+
+    const double range = odiag_max - odiag_min;
+    for (size_t i = 0; i < m; ++i) {
+      const size_t L = n0 + i;   // index of the new species; length of the dense temporaries (:411)
+      const uint32_t p = parents[i];
+      std::vector<double> rw(L, 0.0), cl(L, 0.0);
+      for (size_t j = 0; j < row.size(); ++j) if (row[j] == p) rw[col[j]] = val[j];
+      rw[p] = diag[p];
+      perturb_links(rw, range, odiag_min, gd[i]);
+      for (size_t j = 0; j < col.size(); ++j) if (col[j] == p) cl[row[j]] = val[j];
+      cl[p] = diag[p];
+      perturb_links(cl, range, odiag_min, gd[i]);
+
+      // keep n.beta.n < 0: shave the positive part (:434-446); note diag is indexed by i, as in the reference (:437)
+      double s = 0;
+      std::vector<uint8_t> pos(L);
+      for (size_t q = 0; q < L; ++q) { pos[q] = rw[q] + cl[q] > 0; if (pos[q]) s += rw[q] + cl[q]; }
+      s += diag[i];
+      if (s > 0) {
+        int nadj = 0;
+        for (size_t q = 0; q < L; ++q) nadj += pos[q] && (rw[q] != 0.0 || cl[q] != 0.0);
+        for (size_t q = 0; q < L; ++q) {
+          const bool a = pos[q] && rw[q] != 0.0, b = pos[q] && cl[q] != 0.0;
+          if (a) rw[q] = rw[q] - s / nadj;
+          if (b) cl[q] = cl[q] - s / nadj;
+        }
+      }
+      for (size_t q = 0; q < L; ++q) if (rw[q] != 0.0) { val.push_back(rw[q]); row.push_back((uint32_t)L); col.push_back((uint32_t)q); }
+      for (size_t q = 0; q < L; ++q) if (cl[q] != 0.0) { val.push_back(cl[q]); row.push_back((uint32_t)q); col.push_back((uint32_t)L); }
+    }
+    for (size_t k = 0; k < m; ++k) { create.push_back(0); species.push_back((int32_t)(k * nprocs) + sp_cntr); }
+    sp_cntr += (int)(m * nprocs);
+    beta_dirty = true;
+  }
+
+  void mutate_cells(std::vector<eco::MutRecord>& rec) {
+    check_sizes(false);
+    const size_t n = nsp();
+    if (mutation.size() != n || migration.size() != n || create.size() != n)
+      throw std::runtime_error("inconsistent model: mutation/migration/create size differs from species (call makeConsistent)");
+    std::vector<double> ms(n);
+    const double dt = (double)(tstep - last_mut_tstep);
+    for (size_t s = 0; s < n; ++s) ms[s] = sp_sep * repro_rate[s] * mutation[s] * dt;   // :207 / :218
+    last_mut_tstep = tstep;
+    eng.mutate_cells(ms.data(), tstep, seed, rec);
+  }
+
+  void mutate() {
+    std::vector<eco::MutRecord> rec;
+    mutate_cells(rec);
+    std::vector<uint32_t> parents, cells;
+    for (const auto& r : rec)
+      for (uint32_t k = 0; k < r.count; ++k) { parents.push_back(r.slot); cells.push_back(r.cell); }   // gen_index
+    mutateModel(parents);
+    if (parents.empty()) return;
+    eng.append_species(cells.data(), cells.size());
+  }
+
+  // sparse_mat::init_rand, include/sparse_mat.h:88-111; fill_unique_rand, src/arrays.cc:56-83
+  void random_interaction(unsigned conn, double sigma) {
+    const size_t n = diag.size();
+    if (conn >= n && n) throw std::runtime_error("random_interaction: conn must be smaller than the number of species");
+    std::vector<unsigned> rsize(n);
+    for (size_t i = 0; i < n; ++i) {
+      const double t = g_grand.next() * sigma + (double)conn;
+      rsize[i] = (unsigned)(t > 0 ? t : 0.0);
+    }
+    row.clear(); col.clear();
+    for (size_t i = 0; i < n; ++i) {
+      std::vector<int> pick(std::min<size_t>(rsize[i], n));
+      if (pick.size() > n / 2) {
+        std::vector<double> key(n);
+        for (double& v : key) v = urand01();
+        std::vector<int> deck(n);
+        for (size_t q = 0; q < n; ++q) deck[q] = (int)q;
+        std::sort(deck.begin(), deck.end(), [&](int a, int b) { return key[a] < key[b]; });
+        std::copy(deck.begin(), deck.begin() + pick.size(), pick.begin());
+      } else {
+        std::vector<bool> seen(n);
+        for (size_t q = 0; q < pick.size();) {
+          const size_t j = (size_t)((n * (double)::rand()) / RAND_MAX);
+          if (j < n && !seen[j]) { seen[j] = true; pick[q++] = (int)j; }
+        }
+      }
+      for (int c : pick) if (c != (int)i) { row.push_back((uint32_t)i); col.push_back((uint32_t)c); }
+    }
+    val.assign(row.size(), 0.0);
+    beta_dirty = true;
+  }
+
+  double connectivity() const {   // :317-323
+    if (species.empty()) return 0;
+    double s = 0;
+    for (size_t j = 0; j < val.size(); ++j) s += (val[j] * val[j]) / (diag[row[j]] * diag[col[j]]);
+    return s / (species.size() * (species.size() - 1));
+  }
+};
+
+// ---------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------
+#define ECO_TRY try {
+#define ECO_CATCH                                   \
+  }                                                 \
+  catch (const std::exception& e) {                 \
+    g_err = e.what();                               \
+    return 1;                                       \
+  }                                                 \
+  catch (...) {                                     \
+    g_err = "unknown error";                        \
+    return 1;                                       \
+  }                                                 \
+  return 0;
+
+namespace {
+std::vector<double>* f64_member(eco_model* m, const std::string& n) {
+  if (n == "create") return &m->create;
+  if (n == "repro_rate") return &m->repro_rate;
+  if (n == "mutation") return &m->mutation;
+  if (n == "migration") return &m->migration;
+  if (n == "interaction.diag") return &m->diag;
+  if (n == "interaction.val") return &m->val;
+  return nullptr;
+}
+double* scalar_member(eco_model* m, const std::string& n) {
+  if (n == "sp_sep") return &m->sp_sep;
+  if (n == "mut_max") return &m->mut_max;
+  if (n == "repro_min") return &m->repro_min;
+  if (n == "repro_max") return &m->repro_max;
+  if (n == "odiag_min") return &m->odiag_min;
+  if (n == "odiag_max") return &m->odiag_max;
+  if (n == "gen_bias") return &m->gen_bias;
+  return nullptr;
+}
+template <class T>
+void copy_out(const std::vector<T>& v, T* out, size_t cap, size_t* n) {
+  if (n) *n = v.size();
+  if (out) std::copy(v.begin(), v.begin() + std::min(cap, v.size()), out);
+}
+void need(eco_model* m) {
+  if (!m) throw std::runtime_error("null model handle");
+}
+}  // namespace
+
+extern "C" {
+
+const char* eco_last_error(void) { return g_err.c_str(); }
+const char* eco_version(void) { return "ecolab_b200 0.1 (sm_100a)"; }
+
+int eco_create(eco_model** out, int dev) {
+  ECO_TRY
+  if (!out) throw std::runtime_error("null out pointer");
+  *out = new eco_model(dev);
+  ECO_CATCH
+}
+int eco_destroy(eco_model* m) {
+  ECO_TRY
+  delete m;
+  ECO_CATCH
+}
+int eco_set_stream(eco_model* m, void* s) {
+  ECO_TRY
+  need(m);
+  m->eng.set_stream(s);
+  ECO_CATCH
+}
+int eco_sync(eco_model* m) {
+  ECO_TRY
+  need(m);
+  m->eng.sync();
+  ECO_CATCH
+}
+
+int eco_set_f64(eco_model* m, const char* name, const double* v, size_t n) {
+  ECO_TRY
+  need(m);
+  auto* a = f64_member(m, name);
+  if (!a) throw std::runtime_error(std::string("unknown f64 member: ") + name);
+  a->assign(v, v + n);
+  m->beta_dirty = true;
+  ECO_CATCH
+}
+int eco_get_f64(eco_model* m, const char* name, double* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  auto* a = f64_member(m, name);
+  if (!a) throw std::runtime_error(std::string("unknown f64 member: ") + name);
+  copy_out(*a, out, cap, n);
+  ECO_CATCH
+}
+int eco_set_u32(eco_model* m, const char* name, const uint32_t* v, size_t n) {
+  ECO_TRY
+  need(m);
+  const std::string s(name);
+  if (s == "interaction.row") m->row.assign(v, v + n);
+  else if (s == "interaction.col") m->col.assign(v, v + n);
+  else throw std::runtime_error("unknown u32 member: " + s);
+  m->beta_dirty = true;
+  ECO_CATCH
+}
+int eco_get_u32(eco_model* m, const char* name, uint32_t* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  const std::string s(name);
+  if (s == "interaction.row") copy_out(m->row, out, cap, n);
+  else if (s == "interaction.col") copy_out(m->col, out, cap, n);
+  else throw std::runtime_error("unknown u32 member: " + s);
+  ECO_CATCH
+}
+int eco_set_i32(eco_model* m, const char* name, const int32_t* v, size_t n) {
+  ECO_TRY
+  need(m);
+  if (std::string(name) != "species") throw std::runtime_error(std::string("unknown i32 member: ") + name);
+  m->species.assign(v, v + n);
+  m->beta_dirty = true;
+  ECO_CATCH
+}
+int eco_get_i32(eco_model* m, const char* name, int32_t* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  if (std::string(name) != "species") throw std::runtime_error(std::string("unknown i32 member: ") + name);
+  copy_out(m->species, out, cap, n);
+  ECO_CATCH
+}
+int eco_set_scalar(eco_model* m, const char* name, double v) {
+  ECO_TRY
+  need(m);
+  const std::string s(name);
+  if (double* p = scalar_member(m, s)) *p = v;
+  else if (s == "tstep") m->tstep = (uint64_t)v;
+  else if (s == "last_mut_tstep") m->last_mut_tstep = (uint64_t)v;
+  else if (s == "last_mig_tstep") m->last_mig_tstep = (uint64_t)v;
+  else if (s == "fixMutation") m->fixMutation = v != 0;
+  else if (s == "fixMigration") m->fixMigration = v != 0;
+  else if (s == "nprocs") m->nprocs = (unsigned)v;
+  else throw std::runtime_error("unknown scalar member: " + s);
+  ECO_CATCH
+}
+int eco_get_scalar(eco_model* m, const char* name, double* out) {
+  ECO_TRY
+  need(m);
+  const std::string s(name);
+  if (double* p = scalar_member(m, s)) *out = *p;
+  else if (s == "tstep") *out = (double)m->tstep;
+  else if (s == "last_mut_tstep") *out = (double)m->last_mut_tstep;
+  else if (s == "last_mig_tstep") *out = (double)m->last_mig_tstep;
+  else if (s == "fixMutation") *out = m->fixMutation;
+  else if (s == "fixMigration") *out = m->fixMigration;
+  else if (s == "nsp") *out = (double)std::max(m->nsp(), (size_t)m->eng.nsp());
+  else if (s == "nnz") *out = (double)m->val.size();
+  else if (s == "ncells") *out = (double)(m->numX * m->numY);
+  else if (s == "ncells_local") *out = (double)m->ncells_local();
+  else if (s == "numX") *out = (double)m->numX;
+  else if (s == "numY") *out = (double)m->numY;
+  else if (s == "maxNbrs") *out = (double)m->maxNbrs;
+  else if (s == "launches") *out = (double)m->eng.launches();
+  else if (s == "device_bytes") *out = (double)m->eng.bytes_allocated();
+  else if (s == "nprocs") *out = (double)m->nprocs;
+  else throw std::runtime_error("unknown scalar member: " + s);
+  ECO_CATCH
+}
+
+int eco_set_grid(eco_model* m, size_t nx, size_t ny) {
+  ECO_TRY
+  need(m);
+  m->setGrid(nx, ny, 0, ny);
+  ECO_CATCH
+}
+int eco_set_grid_slab(eco_model* m, size_t nx, size_t ny, size_t y0, size_t nyl) {
+  ECO_TRY
+  need(m);
+  m->setGrid(nx, ny, y0, nyl);
+  ECO_CATCH
+}
+
+int eco_set_density(eco_model* m, size_t cell, const int32_t* d, size_t n) {
+  ECO_TRY
+  need(m);
+  const size_t lc = m->local_cell(cell);
+  for (size_t i = 0; i < n; ++i)
+    if (d[i] < 0) throw std::runtime_error("density must be non-negative (reference asserts density>=0, models/ecolab_model.cc:108)");
+  m->grow_engine(std::max(n, m->nsp()));
+  m->eng.set_density(lc, d, n);
+  ECO_CATCH
+}
+int eco_get_density(eco_model* m, size_t cell, int32_t* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  const size_t lc = m->local_cell(cell);
+  const size_t ns = m->eng.nsp();
+  if (n) *n = ns;
+  if (out && ns) {
+    if (cap >= ns) m->eng.get_density(lc, out, ns);
+    else {
+      std::vector<int32_t> tmp(ns);
+      m->eng.get_density(lc, tmp.data(), ns);
+      std::copy(tmp.begin(), tmp.begin() + cap, out);
+    }
+  }
+  ECO_CATCH
+}
+int eco_set_density_all(eco_model* m, const int32_t* d, size_t ncells, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (ncells != m->ncells_local()) throw std::runtime_error("set_density_all: cell count differs from the owned grid");
+  m->grow_engine(std::max(nsp, m->nsp()));
+  if (nsp != m->eng.nsp()) throw std::runtime_error("set_density_all: species count differs from the model");
+  m->eng.set_density_all(d, nsp);
+  ECO_CATCH
+}
+int eco_get_density_all(eco_model* m, int32_t* out, size_t ncells, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (ncells != m->ncells_local()) throw std::runtime_error("get_density_all: cell count differs from the owned grid");
+  if (nsp != m->eng.nsp()) throw std::runtime_error("get_density_all: species count differs from the model");
+  m->eng.get_density_all(out, nsp);
+  ECO_CATCH
+}
+int eco_set_density_all_device(eco_model* m, const int32_t* d, size_t ncells, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (ncells != m->ncells_local()) throw std::runtime_error("set_density_all_device: cell count differs from the owned grid");
+  m->grow_engine(std::max(nsp, m->nsp()));
+  if (nsp != m->eng.nsp()) throw std::runtime_error("set_density_all_device: species count differs from the model");
+  m->eng.set_density_all_dev(d, nsp);
+  ECO_CATCH
+}
+int eco_get_density_all_device(eco_model* m, int32_t* out, size_t ncells, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (ncells != m->ncells_local()) throw std::runtime_error("get_density_all_device: cell count differs from the owned grid");
+  if (nsp != m->eng.nsp()) throw std::runtime_error("get_density_all_device: species count differs from the model");
+  m->eng.get_density_all_dev(out, nsp);
+  ECO_CATCH
+}
+int eco_fill_density(eco_model* m, int32_t v) {
+  ECO_TRY
+  need(m);
+  if (v < 0) throw std::runtime_error("density must be non-negative");
+  m->grow_engine(m->nsp());
+  m->eng.fill_density(v);
+  ECO_CATCH
+}
+int eco_get_salt(eco_model* m, size_t cell, double* out) {
+  ECO_TRY
+  need(m);
+  *out = (double)philox_host(m->seed, 2, (uint32_t)cell, 0, m->salt_t) / 4294967295.0;   // :619-620
+  ECO_CATCH
+}
+
+int eco_make_consistent(eco_model* m) {
+  ECO_TRY
+  need(m);
+  m->makeConsistent();
+  ECO_CATCH
+}
+int eco_seed(eco_model* m, uint32_t s) {
+  ECO_TRY
+  need(m);
+  m->seed = s;
+  ECO_CATCH
+}
+int eco_generate(eco_model* m, unsigned niter) {
+  ECO_TRY
+  need(m);
+  m->generate(niter);
+  ECO_CATCH
+}
+int eco_migrate(eco_model* m, uint64_t* total) {
+  ECO_TRY
+  need(m);
+  const uint64_t t = m->migrate_local();
+  if (total) *total = t / 2;   // :702
+  ECO_CATCH
+}
+int eco_migrate_local(eco_model* m, uint64_t* total) {
+  ECO_TRY
+  need(m);
+  const uint64_t t = m->migrate_local();
+  if (total) *total = t;
+  ECO_CATCH
+}
+int eco_condense(eco_model* m, unsigned* removed) {
+  ECO_TRY
+  need(m);
+  const unsigned r = m->condense();
+  if (removed) *removed = r;
+  ECO_CATCH
+}
+int eco_mutate(eco_model* m) {
+  ECO_TRY
+  need(m);
+  m->mutate();
+  ECO_CATCH
+}
+int eco_random_interaction(eco_model* m, unsigned conn, double sigma) {
+  ECO_TRY
+  need(m);
+  m->random_interaction(conn, sigma);
+  ECO_CATCH
+}
+int eco_connectivity(eco_model* m, double* out) {
+  ECO_TRY
+  need(m);
+  *out = m->connectivity();
+  ECO_CATCH
+}
+int eco_nsp_per_cell(eco_model* m, uint32_t* out, size_t ncells) {
+  ECO_TRY
+  need(m);
+  if (ncells != m->ncells_local()) throw std::runtime_error("nsp_per_cell: cell count differs from the owned grid");
+  m->eng.nsp_per_cell(out);
+  ECO_CATCH
+}
+int eco_lifetimes(eco_model* m, double* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  if (!m->panmictic) throw std::runtime_error("lifetimes is a panmictic_ecolab method");
+  const size_t ns = m->nsp();
+  std::vector<int32_t> d(ns);
+  if (ns) m->eng.get_density(0, d.data(), std::min<size_t>(ns, m->eng.nsp()));
+  if (m->create.size() != ns) throw std::runtime_error("inconsistent model: create size differs from species");
+  std::vector<double> lt;
+  for (size_t i = 0; i < ns; ++i) {   // :478-488
+    if (m->create[i] == 0 && d[i] > 10) m->create[i] = (double)m->tstep;
+    else if (m->create[i] > 0 && d[i] == 0) { lt.push_back(m->tstep - m->create[i]); m->create[i] = 0; }
+  }
+  copy_out(lt, out, cap, n);
+  ECO_CATCH
+}
+int eco_mutant_connectivity(eco_model* m, size_t before, double* out) {
+  ECO_TRY
+  need(m);
+  const size_t ns = m->nsp();
+  *out = 0;
+  if (ns > before) {   // :496-501
+    double s = 0;
+    for (size_t j = 0; j < m->val.size(); ++j)
+      if (m->row[j] > before || m->col[j] > before) s += (m->val[j] * m->val[j]) / (m->diag[m->row[j]] * m->diag[m->col[j]]);
+    *out = s / ((ns - before) * (ns - 1));
+  }
+  ECO_CATCH
+}
+int eco_extinction_connectivity(eco_model* m, double* out) {
+  ECO_TRY
+  need(m);
+  const size_t ns = m->nsp();
+  std::vector<int32_t> d(ns);
+  if (ns) m->eng.get_density(0, d.data(), std::min<size_t>(ns, m->eng.nsp()));
+  size_t dead = 0;
+  for (int v : d) dead += v == 0;
+  *out = 0;
+  if (dead) {   // :509-514
+    double s = 0;
+    for (size_t j = 0; j < m->val.size(); ++j)
+      if (d[m->row[j]] == 0 || d[m->col[j]] == 0) s += (m->val[j] * m->val[j]) / (m->diag[m->row[j]] * m->diag[m->col[j]]);
+    *out = s / (dead * (ns - 1));
+  }
+  ECO_CATCH
+}
+int eco_species_totals(eco_model* m, int64_t* out, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (nsp != m->eng.nsp()) throw std::runtime_error("species_totals: species count differs from the model");
+  m->eng.species_totals(out);
+  ECO_CATCH
+}
+
+}  // extern "C"
+
+// ---- checkpoint / restart: self-describing little-endian dump -------------------------
+namespace {
+const char kMagic[8] = {'E', 'C', 'O', 'B', '2', '0', '0', 1};
+template <class T> void wr(FILE* f, const T& v) { if (fwrite(&v, sizeof v, 1, f) != 1) throw std::runtime_error("checkpoint: write failed"); }
+template <class T> void rd(FILE* f, T& v) { if (fread(&v, sizeof v, 1, f) != 1) throw std::runtime_error("restart: truncated file"); }
+template <class T> void wrv(FILE* f, const std::vector<T>& v) {
+  wr(f, (uint64_t)v.size());
+  if (!v.empty() && fwrite(v.data(), sizeof(T), v.size(), f) != v.size()) throw std::runtime_error("checkpoint: write failed");
+}
+template <class T> void rdv(FILE* f, std::vector<T>& v) {
+  uint64_t n; rd(f, n);
+  v.resize(n);
+  if (n && fread(v.data(), sizeof(T), n, f) != n) throw std::runtime_error("restart: truncated file");
+}
+}  // namespace
+
+extern "C" {
+
+int eco_checkpoint(eco_model* m, const char* file) {
+  ECO_TRY
+  need(m);
+  FILE* f = fopen(file, "wb");
+  if (!f) throw std::runtime_error(std::string("checkpoint: cannot open ") + file);
+  struct Closer { FILE* f; ~Closer() { fclose(f); } } closer{f};
+  fwrite(kMagic, 1, 8, f);
+  wr(f, (uint8_t)m->panmictic); wr(f, (uint64_t)m->numX); wr(f, (uint64_t)m->numY); wr(f, (uint64_t)m->y0); wr(f, (uint64_t)m->nyl);
+  wr(f, (uint64_t)m->maxNbrs);
+  wr(f, m->tstep); wr(f, m->last_mut_tstep); wr(f, m->last_mig_tstep);
+  wr(f, m->sp_sep); wr(f, m->mut_max); wr(f, m->repro_min); wr(f, m->repro_max); wr(f, m->odiag_min); wr(f, m->odiag_max); wr(f, m->gen_bias);
+  wr(f, (uint8_t)m->fixMutation); wr(f, (uint8_t)m->fixMigration);
+  wr(f, m->seed); wr(f, m->salt_t); wr(f, (int32_t)m->sp_cntr);
+  wrv(f, m->species); wrv(f, m->create); wrv(f, m->repro_rate); wrv(f, m->mutation); wrv(f, m->migration);
+  wrv(f, m->diag); wrv(f, m->val); wrv(f, m->row); wrv(f, m->col);
+  const size_t ns = m->eng.nsp();
+  std::vector<int32_t> d(m->ncells_local() * ns);
+  if (!d.empty()) m->eng.get_density_all(d.data(), ns);
+  wr(f, (uint64_t)ns);
+  wrv(f, d);
+  ECO_CATCH
+}
+int eco_restart(eco_model* m, const char* file) {
+  ECO_TRY
+  need(m);
+  FILE* f = fopen(file, "rb");
+  if (!f) throw std::runtime_error(std::string("restart: cannot open ") + file);
+  struct Closer { FILE* f; ~Closer() { fclose(f); } } closer{f};
+  char magic[8];
+  if (fread(magic, 1, 8, f) != 8 || memcmp(magic, kMagic, 8)) throw std::runtime_error("restart: not an ecolab_b200 checkpoint");
+  uint8_t pan, fm, fg; uint64_t nx, ny, y0, nyl, mn;
+  rd(f, pan); rd(f, nx); rd(f, ny); rd(f, y0); rd(f, nyl); rd(f, mn);
+  rd(f, m->tstep); rd(f, m->last_mut_tstep); rd(f, m->last_mig_tstep);
+  rd(f, m->sp_sep); rd(f, m->mut_max); rd(f, m->repro_min); rd(f, m->repro_max); rd(f, m->odiag_min); rd(f, m->odiag_max); rd(f, m->gen_bias);
+  rd(f, fm); rd(f, fg);
+  m->fixMutation = fm; m->fixMigration = fg;
+  int32_t spc;
+  rd(f, m->seed); rd(f, m->salt_t); rd(f, spc);
+  m->sp_cntr = spc;
+  rdv(f, m->species); rdv(f, m->create); rdv(f, m->repro_rate); rdv(f, m->mutation); rdv(f, m->migration);
+  rdv(f, m->diag); rdv(f, m->val); rdv(f, m->row); rdv(f, m->col);
+  uint64_t ns; rd(f, ns);
+  std::vector<int32_t> d; rdv(f, d);
+  if (pan) {
+    m->panmictic = true; m->numX = m->numY = 1; m->y0 = 0; m->nyl = 1;
+    m->eng.set_grid(1, 1, 0, 1, (uint32_t)ns);
+  } else {
+    m->setGrid(nx, ny, y0, nyl);
+    m->eng.resize_species((uint32_t)ns);
+  }
+  m->maxNbrs = mn;
+  if (ns > m->eng.nsp()) m->eng.resize_species((uint32_t)ns);
+  if (!d.empty()) m->eng.set_density_all(d.data(), ns);
+  m->beta_dirty = true;
+  ECO_CATCH
+}
+
+// ---- multi-GPU halves ---------------------------------------------------------------------
+int eco_halo_ptrs(eco_model* m, void** st, void** sb, void** rt, void** rb, size_t* bytes) {
+  ECO_TRY
+  need(m);
+  m->eng.halo_ptrs(st, sb, rt, rb);
+  if (bytes) *bytes = m->eng.row_bytes();
+  ECO_CATCH
+}
+int eco_ipc_export(eco_model* m, void* h, size_t* o1, size_t* o2) {
+  ECO_TRY
+  need(m);
+  m->eng.ipc_export(h, o1, o2);
+  ECO_CATCH
+}
+int eco_ipc_import(eco_model* m, const void* h, void** base) {
+  ECO_TRY
+  need(m);
+  *base = m->eng.ipc_import(h);
+  ECO_CATCH
+}
+int eco_set_peer_rows(eco_model* m, const void* top, const void* bottom) {
+  ECO_TRY
+  need(m);
+  m->eng.set_peer_rows(top, bottom);
+  ECO_CATCH
+}
+int eco_alive_mask(eco_model* m, uint8_t* alive, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (nsp != m->nsp() || nsp != m->eng.nsp()) throw std::runtime_error("alive_mask: species count differs from the model");
+  if (nsp) m->eng.alive_mask(alive);
+  ECO_CATCH
+}
+int eco_condense_apply(eco_model* m, const uint8_t* alive, size_t nsp, unsigned* removed) {
+  ECO_TRY
+  need(m);
+  if (nsp != m->nsp() || nsp != m->eng.nsp()) throw std::runtime_error("condense_apply: species count differs from the model");
+  const unsigned r = m->condense_apply(std::vector<uint8_t>(alive, alive + nsp));
+  if (removed) *removed = r;
+  ECO_CATCH
+}
+int eco_mutate_cells(eco_model* m, size_t* n) {
+  ECO_TRY
+  need(m);
+  m->mutate_cells(m->pending);
+  if (n) *n = m->pending.size();
+  ECO_CATCH
+}
+int eco_mutate_records(eco_model* m, eco_mut_record* out, size_t cap) {
+  ECO_TRY
+  need(m);
+  if (cap < m->pending.size()) throw std::runtime_error("mutate_records: output buffer too small");
+  static_assert(sizeof(eco_mut_record) == sizeof(eco::MutRecord), "record layout");
+  if (!m->pending.empty()) memcpy(out, m->pending.data(), m->pending.size() * sizeof(eco_mut_record));
+  ECO_CATCH
+}
+int eco_mutate_model(eco_model* m, const uint32_t* parents, size_t n) {
+  ECO_TRY
+  need(m);
+  m->check_sizes(false);
+  if (m->mutation.size() != m->nsp() || m->migration.size() != m->nsp() || m->create.size() != m->nsp())
+    throw std::runtime_error("inconsistent model: mutation/migration/create size differs from species");
+  m->mutateModel(std::vector<uint32_t>(parents, parents + n));
+  ECO_CATCH
+}
+int eco_append_species(eco_model* m, const uint32_t* cells, size_t n) {
+  ECO_TRY
+  need(m);
+  m->eng.append_species(cells, n);
+  ECO_CATCH
+}
+
+void eco_array_urand_seed(int seed) { srand((unsigned)seed); }
+void eco_array_grand_reset(void) { g_grand = RunningClt(); }
+
+int eco_set_tuning(eco_model* m, const char* knob, int value) {
+  ECO_TRY
+  need(m);
+  const std::string k(knob);
+  if (k == "gen_threads") m->eng.gen_variant = value;
+  else if (k == "mig_variant") m->eng.mig_variant = value;
+  else throw std::runtime_error("unknown tuning knob: " + k);
+  ECO_CATCH
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+/* ecolab_b200.h -- C ABI of the B200-native EcoLab population-update engine.
+ *
+ * This is the drop-in boundary for ONE path of highperformancecoder/ecolab: the
+ * ecology model's per-timestep update in models/ecolab_model.cc (generate /
+ * mutate / migrate / condense) plus the model members the driver scripts read
+ * and write.  The reference exposes that path as classdesc-reflected C++
+ * objects (`panmictic_ecolab`, `spatial_ecolab`, models/ecolab_model.cc:32-41);
+ * every entry point below names the reference member it replaces (file:line
+ * relative to the reference checkout).  INTEGRATION.md shows the binding a
+ * reference maintainer would add on top of this header.
+ *
+ * Conventions
+ *   - plain C types only; host buffers are caller-owned, device memory is
+ *     callee-owned; a model handle is bound to one CUDA device.
+ *   - every function returns 0 on success, non-zero on failure;
+ *     eco_last_error() returns the message of the calling thread's last failure
+ *     (the reference throws C++ exceptions that surface as Python exceptions,
+ *     include/error.h:24-49).
+ *   - calls are synchronous at the API unless stated otherwise; one driver
+ *     thread per handle (the reference is driven under the GIL).
+ *   - the engine requires a CUDA device: eco_create fails loudly without one.
+ *     There is no CPU fallback.
+ *   - RNG: counter-based Philox4x32-10, ctr={cell id, slot>>2, t_lo, t_hi},
+ *     key={seed, stage}, stage 0=generate 1=mutate 2=salt.
+ */
+#ifndef ECOLAB_B200_H
+#define ECOLAB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct eco_model eco_model;
+
+/* record of one speciation event batch: `count` mutants of parent `slot` born in global cell `cell` */
+typedef struct eco_mut_record { uint32_t cell, slot, count; } eco_mut_record;
+
+const char* eco_last_error(void);
+const char* eco_version(void);
+
+/* ---- lifetime ------------------------------------------------------------------
+ * A fresh model is panmictic (one cell; reference PanmicticModel,
+ * models/ecolab_model.h:105-121) until eco_set_grid is called (SpatialModel,
+ * models/ecolab_model.h:128-151). */
+int eco_create(eco_model** out, int cuda_device);
+int eco_destroy(eco_model* m);
+/* run all kernels of this model on an existing CUDA stream (cudaStream_t) */
+int eco_set_stream(eco_model* m, void* cuda_stream);
+int eco_sync(eco_model* m);                          /* EcolabGraph::syncThreads, include/ecolab.h:240 */
+
+/* ---- ModelData members (models/ecolab_model.h:47-57) ----------------------------
+ * f64 arrays : "create" "repro_rate" "mutation" "migration"
+ *              "interaction.diag" "interaction.val"       (include/sparse_mat.h:27)
+ * u32 arrays : "interaction.row" "interaction.col"          (include/sparse_mat.h:29)
+ * i32 array  : "species"
+ * scalars    : "tstep" "last_mut_tstep" "last_mig_tstep" "sp_sep" "mut_max"
+ *              "repro_min" "repro_max" "odiag_min" "odiag_max" "gen_bias"
+ *              "fixMutation" "fixMigration"; read-only: "nsp" "nnz" "ncells"
+ *              "numX" "numY" "maxNbrs" "launches" "device_bytes"
+ * get_* with out==NULL returns the length in *n. */
+int eco_set_f64(eco_model* m, const char* member, const double* v, size_t n);
+int eco_get_f64(eco_model* m, const char* member, double* out, size_t cap, size_t* n);
+int eco_set_u32(eco_model* m, const char* member, const uint32_t* v, size_t n);
+int eco_get_u32(eco_model* m, const char* member, uint32_t* out, size_t cap, size_t* n);
+int eco_set_i32(eco_model* m, const char* member, const int32_t* v, size_t n);
+int eco_get_i32(eco_model* m, const char* member, int32_t* out, size_t cap, size_t* n);
+int eco_set_scalar(eco_model* m, const char* member, double v);
+int eco_get_scalar(eco_model* m, const char* member, double* out);
+
+/* ---- grid (SpatialModel::setGrid, models/ecolab_model.cc:580-605) ----------------
+ * cell id = x + nx*y (makeId, models/ecolab_model.h:137); von Neumann
+ * neighbourhood, open boundaries; density reset to zero.  */
+int eco_set_grid(eco_model* m, size_t nx, size_t ny);
+/* multi-GPU: this process owns global rows [y0, y0+ny_local) of the nx x ny grid
+ * (replaces graphcode's partition/distribute, graphcode/graphcode.h:475-482) */
+int eco_set_grid_slab(eco_model* m, size_t nx, size_t ny, size_t y0, size_t ny_local);
+
+/* ---- density (EcolabPoint::density, models/ecolab_model.h:88) ---------------------
+ * `cell` is the GLOBAL cell id and must be owned by this process. */
+int eco_set_density(eco_model* m, size_t cell, const int32_t* d, size_t n);
+int eco_get_density(eco_model* m, size_t cell, int32_t* out, size_t cap, size_t* n);
+/* all owned cells, host buffer cell-major [cell][nsp] in ascending cell id */
+int eco_set_density_all(eco_model* m, const int32_t* d, size_t ncells, size_t nsp);
+int eco_get_density_all(eco_model* m, int32_t* out, size_t ncells, size_t nsp);
+/* same with DEVICE buffers (device-resident pipelines, benchmarks) */
+int eco_set_density_all_device(eco_model* m, const int32_t* d_dev, size_t ncells, size_t nsp);
+int eco_get_density_all_device(eco_model* m, int32_t* out_dev, size_t ncells, size_t nsp);
+int eco_fill_density(eco_model* m, int32_t value);
+int eco_get_salt(eco_model* m, size_t cell, double* out);   /* EcolabPoint::salt, models/ecolab_model.h:87 */
+
+/* ---- the hot path ----------------------------------------------------------------- */
+/* ModelData::makeConsistent :705-716, SpatialModel::makeConsistent :725-735 */
+int eco_make_consistent(eco_model* m);
+/* PanmicticModel::seed / SpatialModel::seed, models/ecolab_model.h:111,144: sets the Philox seed key */
+int eco_seed(eco_model* m, uint32_t seed);
+/* SpatialModel::generate :607-614 / PanmicticModel::generate :49-54 (EcolabPoint::generate :90-112) */
+int eco_generate(eco_model* m, unsigned niter);
+/* SpatialModel::migrate :616-703; *total = sum|delta|/2 over the owned cells' deltas
+ * (single GPU: the reference's return value; multi GPU: sum the UNHALVED locals, see eco_migrate_local) */
+int eco_migrate(eco_model* m, uint64_t* total);
+/* SpatialModel::condense :171-196 / PanmicticModel::condense :161-169; *removed = #extinct species */
+int eco_condense(eco_model* m, unsigned* removed);
+/* SpatialModel::mutate :215-276 / PanmicticModel::mutate :205-213 */
+int eco_mutate(eco_model* m);
+/* ModelData::random_interaction :43-47 (sparse_mat::init_rand, include/sparse_mat.h:88-111) */
+int eco_random_interaction(eco_model* m, unsigned conn, double sigma);
+/* ModelData::connectivity :317-323 */
+int eco_connectivity(eco_model* m, double* out);
+/* SpatialModel::nsp :117-122 (EcolabPoint::nsp :114-115): living species per owned cell */
+int eco_nsp_per_cell(eco_model* m, uint32_t* out, size_t ncells);
+/* PanmicticModel::lifetimes :474-490 */
+int eco_lifetimes(eco_model* m, double* out, size_t cap, size_t* n);
+/* PanmicticModel::mutantConnectivity :493-503, ::extinctionConnectivity :506-516 */
+int eco_mutant_connectivity(eco_model* m, size_t before_nsp, double* out);
+int eco_extinction_connectivity(eco_model* m, double* out);
+/* per-species totals over owned cells (conservation checks, reference :644,:662) */
+int eco_species_totals(eco_model* m, int64_t* out, size_t nsp);
+/* Model<M>::checkpoint / restart, include/ecolab.h:88-94 */
+int eco_checkpoint(eco_model* m, const char* file);
+int eco_restart(eco_model* m, const char* file);
+
+/* ---- building blocks for the multi-GPU driver (one process per GPU) ----------------
+ * The collectives themselves (halo rows, alive-mask all-reduce, mutant all-gather)
+ * run in the host language over NCCL; these calls are the per-rank halves. */
+/* migrate on the owned slab using the ghost rows (or peer rows) as neighbours;
+ * *abs_delta_sum = sum |delta| over owned cells, NOT halved. (:631-664) */
+int eco_migrate_local(eco_model* m, uint64_t* abs_delta_sum);
+/* device pointers + byte size of the two boundary rows to send and the two ghost rows to fill */
+int eco_halo_ptrs(eco_model* m, void** send_top, void** send_bottom, void** recv_top, void** recv_bottom,
+                  size_t* row_bytes);
+/* CUDA-IPC export of the current density buffer and import of a neighbour's;
+ * peer rows, when set, replace the ghost rows in eco_migrate_local (P2P over NVLink). */
+int eco_ipc_export(eco_model* m, void* handle64, size_t* offset_first_row, size_t* offset_last_row);
+int eco_ipc_import(eco_model* m, const void* handle64, void** base_out);
+int eco_set_peer_rows(eco_model* m, const void* top_row, const void* bottom_row);
+/* condense halves: local alive mask (:173-179); apply a global mask (:188-194) */
+int eco_alive_mask(eco_model* m, uint8_t* alive, size_t nsp);
+int eco_condense_apply(eco_model* m, const uint8_t* alive, size_t nsp, unsigned* removed);
+/* mutate halves: per-cell speciation on the owned cells (:224-227, EcolabPoint::mutate :278-314),
+ * records sorted by (cell, slot); then ModelData::mutate (:362-470) on the gathered parent list;
+ * then the density append (:272-275). */
+int eco_mutate_cells(eco_model* m, size_t* nrecords);                      /* runs the kernel, keeps the records */
+int eco_mutate_records(eco_model* m, eco_mut_record* out, size_t cap);      /* copies them out (cap >= nrecords) */
+int eco_mutate_model(eco_model* m, const uint32_t* parents, size_t n);
+int eco_append_species(eco_model* m, const uint32_t* birth_cells, size_t n);
+
+/* ---- module-level state of the reference's `ecolab` module --------------------------
+ * array_urand.seed (include/random_basic.h:15: srand) and the process-wide
+ * array_grand running-CLT generator (src/random.cc:59-64, src/arrays.cc:24-25). */
+void eco_array_urand_seed(int seed);
+void eco_array_grand_reset(void);
+
+/* tuning knob for profiling: generate threads per CTA (256/512/1024, 0=auto) */
+int eco_set_tuning(eco_model* m, const char* knob, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ECOLAB_B200_H */
