@@ -678,6 +678,14 @@ int eco_migrate(eco_model* m, uint64_t* total) {
   if (total) *total = t / 2;   // :702
   ECO_CATCH
 }
+int eco_step(eco_model* m, unsigned niter, uint64_t* total) {
+  ECO_TRY
+  need(m);
+  m->generate(niter);
+  const uint64_t t = m->migrate_local();
+  if (total) *total = t / 2;
+  ECO_CATCH
+}
 int eco_migrate_local(eco_model* m, uint64_t* total) {
   ECO_TRY
   need(m);
@@ -928,8 +936,31 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   need(m);
   const std::string k(knob);
   if (k == "gen_threads") m->eng.gen_variant = value;
+  else if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
   else if (k == "mig_variant") m->eng.mig_variant = value;
   else throw std::runtime_error("unknown tuning knob: " + k);
+  ECO_CATCH
+}
+
+int eco_kernel_times(eco_model* m, double* out, size_t cap, size_t* n) {
+  ECO_TRY
+  need(m);
+  double ms[eco::Engine::K_COUNT];
+  uint64_t cnt[eco::Engine::K_COUNT];
+  m->eng.kernel_times(ms, cnt);
+  std::vector<double> v;
+  for (int k = 0; k < eco::Engine::K_COUNT; ++k) { v.push_back(ms[k]); v.push_back((double)cnt[k]); }
+  copy_out(v, out, cap, n);
+  ECO_CATCH
+}
+int eco_pre_rounding(eco_model* m, double* out, size_t ncells, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (m->tstep == 0) m->makeConsistent();
+  m->check_sizes(false);
+  if (ncells != m->ncells_local() || nsp != m->nsp()) throw std::runtime_error("pre_rounding: shape differs from the model");
+  m->upload();
+  m->eng.pre_rounding(out);
   ECO_CATCH
 }
 

@@ -1,0 +1,326 @@
+"""spatial_ecolab: the grid model (SpatialModel, models/ecolab_model.h:128-151) and its
+multi-GPU driver.
+
+One process per GPU.  The nx x ny cell grid (cell id = x + nx*y, makeId,
+models/ecolab_model.h:137) is split into contiguous row slabs, rank g owning rows
+[g*ny/G, (g+1)*ny/G); this replaces graphcode's round-robin / ParMETIS partition
+(models/ecolab_model.cc:591, graphcode/partition.cc) and its MPI object exchange.
+Species parameters and beta are replicated.  Communication happens only where the
+reference communicates:
+
+  migrate   halo rows (one grid row of densities per side) -- the reference's
+            prepareNeighbours (graphcode/prepare_neighbours.cc:17-72); either NCCL
+            send/recv into ghost rows or direct peer loads over NVLink (CUDA IPC),
+            plus a sum all-reduce of the migration total (:667-672)
+  condense  max all-reduce of the alive mask (MPI_LOR, :182-186)
+  mutate    all-gather of the (cell, parent slot, count) records (:250), rank 0
+            generates the new species' parameters and broadcasts only the appended
+            tails (the reference broadcasts the whole ModelData, :262-263)
+
+The collectives go through ``torch.distributed`` (NCCL on GPUs; gloo works for the
+host-side logic and is what the CPU tests use).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import EcolabError, MutRecord, check
+from .model import EcoList, EcolabModelBase, _Cell, _Member, _ptr
+
+
+def slab_bounds(ny, world, rank):
+    """Rows [y0, y1) owned by `rank` of `world` (balanced, contiguous, ascending)."""
+    return (rank * ny) // world, ((rank + 1) * ny) // world
+
+
+def merge_records(per_rank):
+    """Concatenate per-rank record arrays (each sorted by (cell, slot)) into the global
+    order: ascending cell id, then slot.  Slabs are contiguous ascending cell ranges, so
+    rank order is already global order; a stable sort keeps this true for any partition."""
+    parts = [np.asarray(p, dtype=np.uint32).reshape(-1, 3) for p in per_rank]
+    parts = [p for p in parts if len(p)]
+    if not parts:
+        return np.zeros((0, 3), dtype=np.uint32)
+    rec = np.concatenate(parts)
+    order = np.lexsort((rec[:, 1], rec[:, 0]))
+    return rec[order]
+
+
+def expand_records(rec):
+    """gen_index (include/arrays.h:2477-2486): parent slot / birth cell repeated `count` times."""
+    rec = np.asarray(rec, dtype=np.uint32).reshape(-1, 3)
+    cnt = rec[:, 2].astype(np.int64)
+    return np.repeat(rec[:, 1], cnt).astype(np.uint32), np.repeat(rec[:, 0], cnt).astype(np.uint32)
+
+
+class Comm:
+    """The four exchanges of the distributed model over torch.distributed."""
+
+    def __init__(self, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.group = torch, dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.backend = dist.get_backend(group)
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if self.backend == "nccl" else torch.device("cpu")
+
+    def _t(self, a):
+        return self.torch.from_numpy(np.ascontiguousarray(a)).to(self.dev)
+
+    def allreduce_max_u8(self, mask):
+        t = self._t(mask.astype(np.uint8))
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return t.cpu().numpy()
+
+    def allreduce_sum(self, v):
+        t = self._t(np.array([v], dtype=np.int64))
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        return int(t.cpu()[0])
+
+    def allgather_records(self, rec):
+        rec = np.asarray(rec, dtype=np.uint32).reshape(-1, 3)
+        n = self._t(np.array([len(rec)], dtype=np.int64))
+        counts = [self.torch.zeros_like(n) for _ in range(self.world)]
+        self.dist.all_gather(counts, n, group=self.group)
+        counts = [int(c.cpu()[0]) for c in counts]
+        mx = max(counts)
+        if mx == 0:
+            return [np.zeros((0, 3), dtype=np.uint32)] * self.world
+        pad = np.zeros((mx, 3), dtype=np.int32)
+        pad[: len(rec)] = rec.view(np.int32)
+        t = self._t(pad)
+        outs = [self.torch.zeros_like(t) for _ in range(self.world)]
+        self.dist.all_gather(outs, t, group=self.group)
+        return [o.cpu().numpy().view(np.uint32)[:c] for o, c in zip(outs, counts)]
+
+    def bcast_arrays(self, arrays, src=0):
+        """Broadcast a dict of numpy arrays from `src` (shapes first, then one flat buffer per dtype)."""
+        obj = [arrays if self.rank == src else None]
+        self.dist.broadcast_object_list(obj, src=src, group=self.group)
+        return obj[0]
+
+    def sendrecv_rows(self, send_up, recv_up, send_down, recv_down):
+        """Exchange boundary rows with rank-1 ("up", lower y) and rank+1 ("down").  Tensors alias device memory."""
+        ops = []
+        P2P = self.dist.P2POp
+        if self.rank > 0:
+            ops += [P2P(self.dist.isend, send_up, self.rank - 1, self.group), P2P(self.dist.irecv, recv_up, self.rank - 1, self.group)]
+        if self.rank + 1 < self.world:
+            ops += [P2P(self.dist.isend, send_down, self.rank + 1, self.group), P2P(self.dist.irecv, recv_down, self.rank + 1, self.group)]
+        if ops:
+            for r in self.dist.batch_isend_irecv(ops):
+                r.wait()
+
+
+# ---------------------------------------------------------------------------------
+# The distributed algorithms, written against the per-rank halves ("ops") so that the
+# same code drives the CUDA engine (SpatialModel below) and, in the CPU tests, a
+# numpy/oracle emulation of one rank under gloo.
+#   ops.alive_mask() -> u8[nsp]            ops.condense_apply(mask) -> removed
+#   ops.mutate_cells() -> u32[n,3]         ops.mutate_model(parents)
+#   ops.lengths() / ops.tails(before) / ops.append_tails(tails)
+#   ops.append_species(cells)              ops.migrate_local() -> sum|delta| (not halved)
+#   ops.halo_tensors() -> (send_up, recv_up, send_down, recv_down) or None; ops.halo_done()
+# ---------------------------------------------------------------------------------
+def dist_migrate(ops, comm):
+    """SpatialModel::migrate (models/ecolab_model.cc:616-703) on a row-slab partition."""
+    t = ops.halo_tensors()
+    if t is not None:
+        comm.sendrecv_rows(*t)
+        ops.halo_done()
+    return comm.allreduce_sum(ops.migrate_local()) // 2   # :667-672, :702
+
+
+def dist_condense(ops, comm):
+    """SpatialModel::condense (:171-196): local mask, logical-or all-reduce, identical compaction everywhere."""
+    mask = np.ascontiguousarray(comm.allreduce_max_u8(ops.alive_mask()))
+    return ops.condense_apply(mask)
+
+
+def dist_mutate(ops, comm):
+    """SpatialModel::mutate (:215-276): per-cell speciation, gather of the records, parameter
+    generation on rank 0, broadcast of the appended tails only, density append everywhere."""
+    merged = merge_records(comm.allgather_records(ops.mutate_cells()))
+    parents, cells = expand_records(merged)
+    if len(parents) == 0:
+        return 0
+    before = ops.lengths()
+    tails = None
+    if comm.rank == 0:   # ModelData::mutate on rank 0 only (:251-258): it draws from rank 0's libc stream
+        ops.mutate_model(parents)
+        tails = ops.tails(before)
+    tails = comm.bcast_arrays(tails, src=0)
+    if comm.rank != 0:
+        ops.append_tails(tails)
+    ops.append_species(cells)
+    return len(parents)
+
+
+class _DevMem:
+    """Expose a raw device range to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+
+
+class SpatialModel(EcolabModelBase):
+    """spatial_ecolab.  Single process: the whole grid on one GPU.  Under torch.distributed
+    (world > 1): this rank's row slab, with the exchanges described in the module docstring."""
+
+    _TAILS_F64 = ("create", "repro_rate", "mutation", "migration", "interaction.diag", "interaction.val")
+    _TAILS_U32 = ("interaction.row", "interaction.col")
+
+    def __init__(self, device=0, comm=None):
+        super().__init__(device)
+        self._comm = comm
+        self._nx = self._ny = 1
+        self._y0, self._y1 = 0, 1
+
+    # ---- distribution ------------------------------------------------------------
+    def attach(self, comm):
+        """Join a process group; call before setGrid."""
+        self._comm = comm
+
+    @property
+    def world(self):
+        return self._comm.world if self._comm else 1
+
+    @property
+    def rank(self):
+        return self._comm.rank if self._comm else 0
+
+    def setGrid(self, nx, ny):
+        nx, ny = int(nx), int(ny)
+        self._nx, self._ny = nx, ny
+        if self.world > 1:
+            if ny < self.world:
+                raise EcolabError(f"setGrid: {ny} grid rows cannot be split over {self.world} ranks")
+            self._y0, self._y1 = slab_bounds(ny, self.world, self.rank)
+            check(self._L.eco_set_scalar(self._h, b"nprocs", float(self.world)))
+            check(self._L.eco_set_grid_slab(self._h, nx, ny, self._y0, self._y1 - self._y0))
+        else:
+            self._y0, self._y1 = 0, ny
+            check(self._L.eco_set_grid(self._h, nx, ny))
+
+    def owns(self, i, j):
+        return self._y0 <= j < self._y1
+
+    def cell(self, i, j):
+        return _Cell(self, int(i) + self._nx * int(j))
+
+    def nsp(self):
+        """Living species per owned cell (SpatialModel::nsp, models/ecolab_model.cc:117-122)."""
+        nc = int(self._scalar("ncells_local"))
+        a = np.empty(nc, dtype=np.uint32)
+        if nc:
+            check(self._L.eco_nsp_per_cell(self._h, _ptr(a), nc))
+        return EcoList(a.tolist())
+
+    # graphcode operations that have nothing left to do under a static slab partition
+    def partitionObjects(self):
+        return None
+
+    def distributeObjects(self):
+        return None
+
+    def gather(self):
+        self.syncThreads()
+
+    # ---- per-rank halves over the C ABI ("ops" protocol) -------------------------------
+    def halo_tensors(self):
+        import torch
+        if not int(self._scalar("nsp")):
+            return None
+        st, sb, rt, rb = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        nb = C.c_size_t()
+        check(self._L.eco_halo_ptrs(self._h, C.byref(st), C.byref(sb), C.byref(rt), C.byref(rb), C.byref(nb)))
+        if nb.value == 0:
+            return None
+        dev = torch.device("cuda", self._device)
+        T = lambda p: torch.as_tensor(_DevMem(p.value, nb.value), device=dev)   # noqa: E731
+        self.syncThreads()   # generate ran on the engine's stream; NCCL is enqueued on torch's
+        return T(st), T(rt), T(sb), T(rb)
+
+    def halo_done(self):
+        import torch
+        torch.cuda.current_stream(torch.device("cuda", self._device)).synchronize()
+
+    def migrate_local(self):
+        t = C.c_uint64()
+        check(self._L.eco_migrate_local(self._h, C.byref(t)))
+        return t.value
+
+    def alive_mask(self):
+        ns = int(self._scalar("nsp"))
+        mask = np.zeros(ns, dtype=np.uint8)
+        if ns:
+            check(self._L.eco_alive_mask(self._h, _ptr(mask), ns))
+        return mask
+
+    def condense_apply(self, mask):
+        r = C.c_uint()
+        check(self._L.eco_condense_apply(self._h, _ptr(mask), len(mask), C.byref(r)))
+        return r.value
+
+    def mutate_cells(self):
+        n = C.c_size_t()
+        check(self._L.eco_mutate_cells(self._h, C.byref(n)))
+        rec = (MutRecord * max(n.value, 1))()
+        if n.value:
+            check(self._L.eco_mutate_records(self._h, rec, n.value))
+        return np.frombuffer(rec, dtype=np.uint32).reshape(-1, 3)[: n.value].copy()
+
+    def mutate_model(self, parents):
+        parents = np.ascontiguousarray(parents, dtype=np.uint32)
+        check(self._L.eco_mutate_model(self._h, _ptr(parents), len(parents)))
+
+    def lengths(self):
+        d = {n: self._array_len(n, "f64") for n in self._TAILS_F64}
+        d.update({n: self._array_len(n, "u32") for n in self._TAILS_U32})
+        d["species"] = self._array_len("species", "i32")
+        return d
+
+    def tails(self, before):
+        t = {k: self._get_array(k, "f64")[before[k]:] for k in self._TAILS_F64}
+        t.update({k: self._get_array(k, "u32")[before[k]:] for k in self._TAILS_U32})
+        t["species"] = self._get_array("species", "i32")[before["species"]:]
+        return t
+
+    def append_tails(self, tails):
+        for k in self._TAILS_F64:
+            self._set_array(k, "f64", np.concatenate([self._get_array(k, "f64"), tails[k]]))
+        for k in self._TAILS_U32:
+            self._set_array(k, "u32", np.concatenate([self._get_array(k, "u32"), tails[k]]))
+        self._set_array("species", "i32", np.concatenate([self._get_array("species", "i32"), tails["species"]]))
+
+    def append_species(self, cells):
+        cells = np.ascontiguousarray(cells, dtype=np.uint32)
+        check(self._L.eco_append_species(self._h, _ptr(cells), len(cells)))
+
+    # ---- the reflected methods ---------------------------------------------------------------
+    def migrate(self):
+        if self.world == 1:
+            t = C.c_uint64()
+            check(self._L.eco_migrate(self._h, C.byref(t)))
+            return t.value
+        return dist_migrate(self, self._comm)
+
+    def step(self, niter=1):
+        """generate(niter) then migrate(); returns migrate's total."""
+        if self.world == 1:
+            t = C.c_uint64()
+            check(self._L.eco_step(self._h, int(niter), C.byref(t)))
+            return t.value
+        self.generate(niter)
+        return self.migrate()
+
+    def condense(self):
+        if self.world == 1:
+            return super().condense()
+        return dist_condense(self, self._comm)
+
+    def mutate(self):
+        if self.world == 1:
+            return super().mutate()
+        dist_mutate(self, self._comm)

@@ -101,6 +101,9 @@ int eco_generate(eco_model* m, unsigned niter);
 /* SpatialModel::migrate :616-703; *total = sum|delta|/2 over the owned cells' deltas
  * (single GPU: the reference's return value; multi GPU: sum the UNHALVED locals, see eco_migrate_local) */
 int eco_migrate(eco_model* m, uint64_t* total);
+/* one driver-loop body of the spatial scripts (models/spatial_ecolab.py:67-69 minus mutate):
+ * eco_generate(niter) followed by eco_migrate(total) as one call (fewer host round trips) */
+int eco_step(eco_model* m, unsigned niter, uint64_t* total);
 /* SpatialModel::condense :171-196 / PanmicticModel::condense :161-169; *removed = #extinct species */
 int eco_condense(eco_model* m, unsigned* removed);
 /* SpatialModel::mutate :215-276 / PanmicticModel::mutate :205-213 */
@@ -153,8 +156,15 @@ int eco_append_species(eco_model* m, const uint32_t* birth_cells, size_t n);
 void eco_array_urand_seed(int seed);
 void eco_array_grand_reset(void);
 
-/* tuning knob for profiling: generate threads per CTA (256/512/1024, 0=auto) */
+/* tuning / profiling knobs: "gen_threads" (256/512/1024, 0=auto), "mig_variant",
+ * "timing" (1 = record a CUDA-event pair around every generate/migrate launch, 0 = off and reset) */
 int eco_set_tuning(eco_model* m, const char* knob, int value);
+/* device time per kernel kind since timing was switched on: out = {generate_ms, generate_launches,
+ * migrate_ms, migrate_launches, ...}; *n = number of doubles available */
+int eco_kernel_times(eco_model* m, double* out, size_t cap, size_t* n);
+/* x = n + n*(r + beta.n) of ONE generate sub-step BEFORE EcolabPoint::ROUND (:99-102), cell-major
+ * [cell][nsp] for the owned cells; densities and tstep are not changed (float-tolerance check) */
+int eco_pre_rounding(eco_model* m, double* out, size_t ncells, size_t nsp);
 
 #ifdef __cplusplus
 }

@@ -116,6 +116,12 @@ struct Oracle {
   // scratch for the float-tolerance test: x before ROUND of the last generate sub-step
   bool record_pre = false;
   std::vector<Float> pre;   // [cell][nsp]
+  // row-slab view used by the multi-rank CPU tests: this instance holds global rows [y0, y0+nyl)
+  // of the numX x numY grid; ghost rows carry the neighbouring slabs' boundary rows for migrate
+  size_t y0 = 0, nyl = 1;
+  std::vector<int32_t> ghost_top, ghost_bottom;   // [numX][nsp]
+  struct Rec { uint32_t cell, slot, count; };
+  std::vector<Rec> pending;
 
   Oracle() { cells.resize(1); }   // panmictic: the model *is* one cell (models/ecolab_model.h:105)
 
@@ -170,6 +176,100 @@ struct Oracle {
         if (j < ny - 1) c.nbr.push_back((uint32_t)(i + nx * (j + 1)));
       }
     for (auto& c : cells) maxNbrs = std::max(maxNbrs, c.nbr.size());   // never shrinks
+  }
+
+  // The same grid, but only rows [y0_, y0_+nyl_) live here (cell ids stay global: x + nx*y).
+  // In-slab neighbours as in setGrid; the rows above/below come from ghost_top/ghost_bottom.
+  void setGridSlab(size_t nx, size_t ny, size_t y0_, size_t nyl_) {
+    panmictic = false;
+    numX = nx; numY = ny; y0 = y0_; nyl = nyl_;
+    cells.assign(nx * nyl, Cell());
+    for (size_t j = 0; j < nyl; ++j)
+      for (size_t i = 0; i < nx; ++i) {
+        Cell& c = cells[i + nx * j];
+        c.id = (uint32_t)(i + nx * (y0 + j));
+        c.mt.seed(c.id);
+      }
+    const size_t nb = std::min<size_t>(nx - 1, 2) + std::min<size_t>(ny - 1, 2);
+    maxNbrs = std::max(maxNbrs, nb);
+  }
+
+  // per-rank half of migrate (:631-664) on a slab: neighbours W,E,N,S in the reference's order
+  // (:593-600: x-1, x+1, y-1, y+1), rows outside the slab read from the ghost rows
+  uint64_t migrateLocal() {
+    const size_t ns = nsp();
+    std::vector<Float> cm(ns);
+    const Float cap = 1.0 / maxNbrs;
+    for (size_t s = 0; s < ns; ++s) {
+      const Float mm = (tstep - last_mig_tstep) * migration[s];
+      cm[s] = mm > cap ? cap : mm;
+    }
+    std::vector<std::vector<int32_t>> delta(cells.size(), std::vector<int32_t>(ns, 0));
+    auto nbr = [&](long x, long yl) -> const int32_t* {   // yl relative to the slab
+      if (yl < 0) return ghost_top.data() + (size_t)x * ns;
+      if (yl >= (long)nyl) return ghost_bottom.data() + (size_t)x * ns;
+      return cells[x + numX * yl].n.data();
+    };
+    for (long yl = 0; yl < (long)nyl; ++yl)
+      for (long x = 0; x < (long)numX; ++x) {
+        const size_t ci = x + numX * yl;
+        const long yg = (long)y0 + yl;
+        const int32_t* own = cells[ci].n.data();
+        const int32_t* nb[4] = {x > 0 ? nbr(x - 1, yl) : nullptr, x < (long)numX - 1 ? nbr(x + 1, yl) : nullptr,
+                                yg > 0 ? nbr(x, yl - 1) : nullptr, yg < (long)numY - 1 ? nbr(x, yl + 1) : nullptr};
+        for (int k = 0; k < 4; ++k)
+          if (nb[k])
+            for (size_t s = 0; s < ns; ++s) delta[ci][s] += (int32_t)(cm[s] * (nb[k][s] - own[s]));
+      }
+    uint64_t total = 0;
+    for (size_t ci = 0; ci < cells.size(); ++ci)
+      for (size_t s = 0; s < ns; ++s) { cells[ci].n[s] += delta[ci][s]; total += (uint64_t)std::abs(delta[ci][s]); }
+    last_mig_tstep = tstep;
+    return total;
+  }
+
+  // per-rank halves of condense (:173-179 mask, :188-194 apply)
+  void aliveMask(uint8_t* mask) {
+    const size_t ns = nsp();
+    for (size_t s = 0; s < ns; ++s) mask[s] = 0;
+    for (auto& c : cells)
+      for (size_t s = 0; s < c.n.size() && s < ns; ++s) if (c.n[s]) mask[s] = 1;
+  }
+  unsigned condenseApply(const uint8_t* m) {
+    const size_t ns = nsp();
+    std::vector<char> mask(m, m + ns);
+    size_t ntrue = 0; for (char b : mask) ntrue += b ? 1 : 0;
+    if (ntrue == ns) return 0;
+    condenseModel(mask);
+    for (auto& c : cells) {
+      std::vector<int32_t> r;
+      for (size_t s = 0; s < c.n.size(); ++s) if (mask[s] && r.size() < ntrue) r.push_back(c.n[s]);
+      c.n.swap(r);
+    }
+    return (unsigned)(ns - ntrue);
+  }
+
+  // per-rank halves of mutate: :224-227 (cells), then the density append :272-275
+  void mutateCells() {
+    const size_t ns = nsp();
+    std::vector<Float> ms(ns);
+    for (size_t s = 0; s < ns; ++s)
+      ms[s] = sp_sep * repro_rate[s] * mutation[s] * Float(tstep - last_mut_tstep);
+    last_mut_tstep = tstep;
+    pending.clear();
+    for (auto& c : cells) {
+      if (c.n.empty()) continue;
+      std::vector<uint32_t> spec(c.n.size());
+      uint64_t tot = 0;
+      for (size_t s = 0; s < c.n.size(); ++s) { spec[s] = (uint32_t)ROUND(ms[s] * c.n[s], c, ST_MUTATE, (uint32_t)s, tstep); tot += spec[s]; }
+      if (!tot) continue;
+      for (size_t s = 0; s < c.n.size(); ++s)
+        if (spec[s]) { c.n[s] -= (int32_t)spec[s]; pending.push_back(Rec{c.id, (uint32_t)s, spec[s]}); }
+    }
+  }
+  void appendSpecies(const uint32_t* ids, size_t m) {
+    for (auto& c : cells)
+      for (size_t k = 0; k < m; ++k) c.n.push_back(ids[k] == c.id ? 1 : 0);
   }
 
   // models/ecolab_model.cc:90-112 EcolabPoint::generate; :607-614 / :49-54 callers
@@ -562,6 +662,19 @@ long orc_get_species(void* h, int32_t* p, size_t cap) {
 }
 
 void orc_set_grid(void* h, size_t nx, size_t ny) { ((Oracle*)h)->setGrid(nx, ny); }
+void orc_set_grid_slab(void* h, size_t nx, size_t ny, size_t y0, size_t nyl) { ((Oracle*)h)->setGridSlab(nx, ny, y0, nyl); }
+uint64_t orc_migrate_local(void* h) { return ((Oracle*)h)->migrateLocal(); }
+void orc_set_ghost(void* h, int bottom, const int32_t* p, size_t n) {
+  auto o = (Oracle*)h; (bottom ? o->ghost_bottom : o->ghost_top).assign(p, p + n);
+}
+void orc_alive_mask(void* h, uint8_t* mask) { ((Oracle*)h)->aliveMask(mask); }
+unsigned orc_condense_apply(void* h, const uint8_t* mask) { return ((Oracle*)h)->condenseApply(mask); }
+size_t orc_mutate_cells(void* h) { auto o = (Oracle*)h; o->mutateCells(); return o->pending.size(); }
+void orc_mutate_records(void* h, uint32_t* out) {
+  auto o = (Oracle*)h;
+  for (size_t i = 0; i < o->pending.size(); ++i) { out[3 * i] = o->pending[i].cell; out[3 * i + 1] = o->pending[i].slot; out[3 * i + 2] = o->pending[i].count; }
+}
+void orc_append_species(void* h, const uint32_t* ids, size_t m) { auto o = (Oracle*)h; o->computeODiagIdx(); o->appendSpecies(ids, m); }
 void orc_set_density(void* h, size_t cell, const int32_t* p, size_t n) { ((Oracle*)h)->cells[cell].n.assign(p, p + n); }
 long orc_get_density(void* h, size_t cell, int32_t* p, size_t cap) {
   auto& v = ((Oracle*)h)->cells[cell].n;

@@ -53,6 +53,14 @@ def lib():
             "orc_get_species": (C.c_long, [vp, vp, sz]),
             "orc_set_grid": (None, [vp, sz, sz]),
             "orc_set_density": (None, [vp, sz, vp, sz]),
+            "orc_set_grid_slab": (None, [vp, sz, sz, sz, sz]),
+            "orc_migrate_local": (u64, [vp]),
+            "orc_set_ghost": (None, [vp, C.c_int, vp, sz]),
+            "orc_alive_mask": (None, [vp, vp]),
+            "orc_condense_apply": (C.c_uint, [vp, vp]),
+            "orc_mutate_cells": (sz, [vp]),
+            "orc_mutate_records": (None, [vp, vp]),
+            "orc_append_species": (None, [vp, vp, sz]),
             "orc_get_density": (C.c_long, [vp, sz, vp, sz]),
             "orc_set_density_all": (None, [vp, vp, sz]),
             "orc_get_density_all": (None, [vp, vp, sz]),
@@ -145,6 +153,37 @@ class Oracle:
     # --- grid / density ----------------------------------------------------
     def set_grid(self, nx, ny):
         self.L.orc_set_grid(self.h, nx, ny)
+
+    # --- row-slab halves (multi-rank CPU tests) -------------------------------
+    def set_grid_slab(self, nx, ny, y0, nyl):
+        self.L.orc_set_grid_slab(self.h, nx, ny, y0, nyl)
+
+    def migrate_local(self):
+        return int(self.L.orc_migrate_local(self.h))
+
+    def set_ghost(self, bottom, rows):
+        a = np.ascontiguousarray(rows, dtype=np.int32)
+        self.L.orc_set_ghost(self.h, int(bottom), _ptr(a), a.size)
+
+    def alive_mask(self):
+        a = np.zeros(self.nsp, dtype=np.uint8)
+        self.L.orc_alive_mask(self.h, _ptr(a))
+        return a
+
+    def condense_apply(self, mask):
+        a = np.ascontiguousarray(mask, dtype=np.uint8)
+        return int(self.L.orc_condense_apply(self.h, _ptr(a)))
+
+    def mutate_cells(self):
+        n = self.L.orc_mutate_cells(self.h)
+        a = np.zeros((n, 3), dtype=np.uint32)
+        if n:
+            self.L.orc_mutate_records(self.h, _ptr(a))
+        return a
+
+    def append_species(self, cells):
+        a = np.ascontiguousarray(cells, dtype=np.uint32)
+        self.L.orc_append_species(self.h, _ptr(a), a.size)
 
     def set_density(self, cell, d):
         a = np.ascontiguousarray(d, dtype=np.int32)

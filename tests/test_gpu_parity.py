@@ -1,0 +1,253 @@
+"""GPU: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): integer densities bit-exact for generate + migrate + condense under the
+shared Philox stream; the pre-rounding float update within 1e-6 relative (here: exactly equal, the kernel
+keeps the reference's FP64 operation order); mutation statistically equivalent (and, because product and
+oracle draw from the same libc rand() stream inside this process, also bit-equal when re-seeded alike).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import SCALARS, densities, gpu_density, load_gpu, load_oracle, oracle_density, synth
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+# (grid, nsp, nnz/row): ragged shapes on purpose -- nx not a multiple of the 32-cell tile, nsp not a multiple of 4
+SHAPES = [
+    (None, 2, 1), (None, 100, 3), (None, 1, 0), (None, 1023, 5),
+    ((1, 1), 7, 2), ((2, 2), 30, 3), ((8, 5), 37, 3), ((33, 3), 64, 16), ((64, 2), 9, 8), ((70, 9), 129, 3),
+    ((31, 1), 5, 0), ((1, 40), 12, 4),
+]
+
+
+def pair(oracle_mod, gpu, grid, nsp, k, seed=5, **kw):
+    ncells = grid[0] * grid[1] if grid else 1
+    p = synth(nsp, k, seed, **kw)
+    d = densities(ncells, nsp, seed)
+    return load_oracle(oracle_mod, p, d, grid, seed=seed), load_gpu(gpu, p, d, grid, seed=seed), grid
+
+
+@pytest.mark.parametrize("grid,nsp,k", SHAPES)
+def test_generate_bit_exact(oracle_mod, gpu, grid, nsp, k):
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k)
+    for niter in (1, 1, 3, 10):        # niter==1: single-pass kernel; niter>1: fused multi-step kernel
+        o.generate(niter); m.generate(niter)
+        assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid)), f"niter={niter}"
+        assert m.tstep() == int(o.get("tstep"))
+
+
+@pytest.mark.parametrize("grid,nsp,k", [(None, 100, 3), ((8, 5), 37, 3), ((33, 3), 64, 16)])
+def test_pre_rounding_float_update(oracle_mod, gpu, grid, nsp, k):
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k)
+    o.generate(2); m.generate(2)
+    x_gpu = m.pre_rounding()
+    o.set("record_pre", 1); o.generate(1)
+    x_cpu = o.pre_rounding().reshape(x_gpu.shape)
+    rel = np.abs(x_gpu - x_cpu) / np.maximum(np.abs(x_cpu), 1e-300)
+    assert rel.max() <= 1e-6            # the stated tolerance
+    assert np.array_equal(x_gpu, x_cpu)  # and in fact identical: same operation order, no FMA
+
+
+def test_generate_round_extremes(oracle_mod, gpu):
+    """ROUND's three branches (models/ecolab_model.cc:57-66): x<=0 -> 0, x>=INT_MAX-1 -> INT_MAX-1, else stochastic."""
+    nsp = 8
+    p = synth(nsp, 2, 9)
+    p["repro_rate"] = np.array([5.0, -3.0, 0.5, -1.0, 0.0, 1e-9, 0.999, -0.999])
+    p["interaction.diag"] = np.zeros(nsp); p["interaction.val"][:] = 0
+    d = np.array([[2 ** 31 - 2, 50, 2 ** 30, 17, 0, 1, 2 ** 31 - 2, 3]] * 40, dtype=np.int32)
+    o = load_oracle(oracle_mod, p, d, (40, 1), seed=3); m = load_gpu(gpu, p, d, (40, 1), seed=3)
+    for _ in range(3):
+        o.generate(1); m.generate(1)
+        assert np.array_equal(m.density_array(), o.get_density_all())
+    got = m.density_array()
+    assert (got[:, 0] == 2 ** 31 - 2).all() and (got[:, 1] == 0).all() and (got[:, 3] == 0).all()
+
+
+@pytest.mark.parametrize("grid,nsp,k", [s for s in SHAPES if s[0]])
+def test_migrate_bit_exact_and_conserves(oracle_mod, gpu, grid, nsp, k):
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k, mig=0.07)
+    for it in range(3):
+        o.generate(1 + it); m.generate(1 + it)
+        before = m.species_totals()
+        mv_o, mv_g = o.migrate(), m.migrate()
+        assert mv_g == mv_o
+        dg = m.density_array()
+        assert np.array_equal(dg, o.get_density_all())
+        assert np.array_equal(m.species_totals(), before) and (dg >= 0).all()   # test/00/spatial_ecolab.sh:56-77
+        assert m.last_mig_tstep() == m.tstep()
+
+
+def test_migrate_cap_and_per_species_rates(oracle_mod, gpu):
+    """cm = min(dt*migration, 1/maxNbrs) (:626-629): huge rates are capped so a cell is never overdrawn."""
+    grid, nsp = (9, 6), 11
+    p = synth(nsp, 2, 4)
+    p["migration"] = np.array([0, 1e-3, 0.1, 0.24, 0.25, 0.26, 1.0, 50.0, 1e-9, 0.2, 0.05])
+    d = densities(54, nsp, 4, dmax=100000)
+    o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
+    for _ in range(4):
+        o.generate(3); m.generate(3)
+        assert m.migrate() == o.migrate()
+        assert np.array_equal(m.density_array(), o.get_density_all())
+    assert (m.density_array() >= 0).all()
+
+
+def test_step_equals_generate_then_migrate(oracle_mod, gpu):
+    o, m, grid = pair(oracle_mod, gpu, (40, 7), 50, 3, mig=0.1)
+    for niter in (1, 4):
+        o.generate(niter); mv = o.migrate()
+        assert m.step(niter) == mv
+        assert np.array_equal(m.density_array(), o.get_density_all())
+
+
+@pytest.mark.parametrize("grid,nsp,k", [(None, 100, 3), ((8, 5), 37, 3), ((70, 9), 129, 3)])
+def test_condense_bit_exact(oracle_mod, gpu, grid, nsp, k):
+    ncells = grid[0] * grid[1] if grid else 1
+    p = synth(nsp, k, 6)
+    d = densities(ncells, nsp, 6)
+    d[:, [0, nsp // 2, nsp - 1]] = 0
+    d[:, 3] = 0
+    o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
+    o.generate(2); m.generate(2)
+    assert m.condense() == o.condense() == 4
+    assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+    for name in ("repro_rate", "mutation", "migration", "create"):
+        assert np.array_equal(np.array(getattr(m, name)()), o.get(name))
+    for name in ("diag", "val", "row", "col"):
+        assert np.array_equal(np.array(getattr(m.interaction, name)()), o.get("interaction." + name)), name
+    assert m.species() == o.get("species").tolist()
+    assert m.condense() == o.condense() == 0
+    o.generate(5); m.generate(5)           # the compacted beta drives the next steps identically
+    assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+
+
+def test_condense_sh(gpu):
+    """test/00/condense.sh:14-21 through the reference-facing API."""
+    m = gpu.PanmicticModel(0)
+    m.density([1, 0, 1, 0, 1])
+    m.makeConsistent()
+    m.repro_rate([1, 1, 1, 1, 1])
+    m.interaction.diag([1, 1, 1, 1, 1])
+    m.condense()
+    assert m.density() == [1, 1, 1]
+
+
+@pytest.mark.parametrize("grid,nsp", [(None, 60), ((8, 5), 37), ((70, 9), 40)])
+def test_mutate_same_streams_bit_exact(oracle_mod, gpu, grid, nsp):
+    """Cell side: same Philox stream -> same speciation counts.  Species side (ModelData::mutate): product and oracle
+    both consume libc rand(); re-seeding before each makes the parameter draws identical too."""
+    O = oracle_mod
+    ncells = grid[0] * grid[1] if grid else 1
+    p = synth(nsp, 3, 8, mut=0.02)
+    scal = dict(SCALARS, mut_max=0.02)
+    d = densities(ncells, nsp, 8)
+    o = load_oracle(O, p, d, grid, scalars=scal); m = load_gpu(gpu, p, d, grid, scalars=scal)
+    for it in range(3):
+        o.generate(3); m.generate(3)
+        O.srand(100 + it); O.reset_grand(); o.mutate()
+        O.srand(100 + it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        assert len(m.species) == o.nsp and o.nsp > nsp
+        assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+        for name in ("repro_rate", "mutation", "migration", "create"):
+            assert np.array_equal(np.array(getattr(m, name)()), o.get(name)), name
+        for name in ("diag", "val", "row", "col"):
+            assert np.array_equal(np.array(getattr(m.interaction, name)()), o.get("interaction." + name)), name
+        assert m.species() == o.get("species").tolist()
+        assert m.last_mut_tstep() == m.tstep()
+    o.generate(2); m.generate(2)
+    assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+
+
+def test_mutate_distribution_ks(oracle_mod, gpu):
+    """Statistical equivalence with DIFFERENT random streams (north_star: KS on species counts and traits)."""
+    from scipy.stats import ks_2samp
+    O = oracle_mod
+    nsp, grid = 50, (16, 16)
+    p = synth(nsp, 3, 12, mut=0.01)
+    scal = dict(SCALARS, mut_max=0.01)
+    d = densities(256, nsp, 12)
+    counts_o, counts_g, r_o, r_g = [], [], [], []
+    for trial in range(12):
+        o = load_oracle(O, p, d, grid, seed=1000 + trial, scalars=scal)
+        m = load_gpu(gpu, p, d, grid, seed=5000 + trial, scalars=scal)
+        o.set("tstep", 10); m.tstep(10)
+        O.srand(trial); o.mutate()
+        O.srand(777 + trial); m.mutate()
+        counts_o.append(o.nsp - nsp); counts_g.append(len(m.species) - nsp)
+        r_o += list(o.get("repro_rate")[nsp:]); r_g += list(m.repro_rate()[nsp:])
+    assert min(counts_o) > 0 and min(counts_g) > 0
+    assert ks_2samp(counts_o, counts_g).pvalue > 0.01
+    assert ks_2samp(r_o, r_g).pvalue > 0.01
+
+
+def test_golden_fixtures(gpu):
+    """The committed fixtures (tests/golden/*.npz, made by tests/golden/make_golden.py from the oracle)."""
+    from golden.make_golden import CASES, case_inputs, run_script
+    for name in CASES:
+        grid, p, d, script = case_inputs(name)
+        m = load_gpu(gpu, p, d, grid, seed=10 + len(name))
+        ops = {"generate": m.generate, "migrate": getattr(m, "migrate", None), "condense": m.condense,
+               "density": lambda: gpu_density(m, grid)}
+        got = run_script(ops, script)
+        want = np.load(os.path.join(GOLDEN, name + ".npz"))
+        for k in want.files:
+            assert np.array_equal(want[k], got[k]), (name, k)
+
+
+def test_script_cadence_matches_oracle(oracle_mod, gpu):
+    """models/spatial_ecolab.py:66-78 cadence: generate(100); mutate(); migrate(); condense() -- several rounds."""
+    O = oracle_mod
+    grid, nsp = (12, 12), 100
+    p = synth(nsp, 3, 21, mut=1e-4)
+    scal = dict(SCALARS, mut_max=1e-4)
+    d = densities(144, nsp, 21, kind="const")
+    o = load_oracle(O, p, d, grid, scalars=scal); m = load_gpu(gpu, p, d, grid, scalars=scal)
+    for it in range(4):
+        o.generate(100); m.generate(100)
+        O.srand(it); O.reset_grand(); o.mutate()
+        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        assert m.migrate() == o.migrate()
+        assert m.condense() == o.condense()
+        assert np.array_equal(m.density_array(), o.get_density_all()), it
+        assert m.nsp() == o.nsp_per_cell().tolist()
+        assert abs(m.connectivity() - o.connectivity()) <= 1e-15 * max(1.0, abs(o.connectivity()))
+
+
+def test_checkpoint_restart_roundtrip(oracle_mod, gpu, tmp_path):
+    """test/checkpoint-restart.sh:38-76: density, repro_rate, interaction.{diag,val,row,col} survive; and because
+    Philox is stateless the restarted run continues bit-identically (the reference excludes its RNG state)."""
+    o, m, grid = pair(oracle_mod, gpu, (8, 5), 37, 3)
+    m.generate(3); m.migrate()
+    f = str(tmp_path / "ck.bin")
+    m.checkpoint(f)
+    m2 = gpu.SpatialModel(0)
+    m2.restart(f)
+    assert np.array_equal(m2.density_array(), m.density_array())
+    for name in ("diag", "val", "row", "col"):
+        assert getattr(m2.interaction, name)() == getattr(m.interaction, name)()
+    assert m2.repro_rate() == m.repro_rate() and m2.tstep() == m.tstep()
+    m.generate(4); m2.generate(4)
+    assert m.migrate() == m2.migrate()
+    assert np.array_equal(m2.density_array(), m.density_array())
+
+
+def test_errors_surface_as_exceptions(gpu):
+    m = gpu.SpatialModel(0)
+    m.species(range(4)); m.setGrid(3, 3)
+    with pytest.raises(gpu.EcolabError):
+        m.generate(1)                       # repro_rate / diag missing
+    with pytest.raises(gpu.EcolabError):
+        m.cell(5, 5).density([1, 2, 3, 4])  # outside the grid
+    with pytest.raises(gpu.EcolabError):
+        m.cell(0, 0).density([-1, 0, 0, 0])
+
+
+def test_empty_model_is_harmless(gpu):
+    m = gpu.SpatialModel(0)
+    m.setGrid(4, 4)
+    m.generate(1)
+    assert m.migrate() == 0 and m.condense() == 0
+    m.mutate()
+    assert m.nsp() == [0] * 16
