@@ -109,6 +109,7 @@ def cpu_leg(nsp, nnz, steps, warmup, budget_s=20.0):
     ny = int(max(8, min(4096, target_updates / (nx * nsp))))
     d = np.full((nx * ny, nsp), 100, dtype=np.int32)
     o = load_oracle(O, p, d, (nx, ny), seed=10)
+    o.fill_density_random(0, 199)    # the same synthetic state as the GPU arm
     for _ in range(warmup):
         o.generate(1); o.migrate()
     t0 = time.perf_counter()
@@ -166,7 +167,7 @@ def build_model(E, args, nx, ny, comm, device, stream):
             getattr(m, k)(v)
     m.setGrid(nx, ny)
     m.seed(10)
-    m.fill_density(100)
+    m.fill_density_random(0, 199)   # mean 100, with gradients between neighbours so migrate really moves population
     return m
 
 
@@ -274,7 +275,7 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     nx = ny = args.e2e_n
     m = build_model(E, args, nx, ny, comm, local, stream)
     nloc = (m._y1 - m._y0) * nx
-    host_in = torch.full((nloc, args.nsp), 100, dtype=torch.int32).pin_memory()
+    host_in = torch.randint(0, 200, (nloc, args.nsp), dtype=torch.int32).pin_memory()
     host_out = torch.empty((nloc, args.nsp), dtype=torch.int32).pin_memory()
     a_in, a_out = host_in.numpy(), host_out.numpy()
     import ctypes as C

@@ -48,6 +48,7 @@ SIGNATURES = {
     "eco_set_density_all_device": [_vp, _vp, _sz, _sz],
     "eco_get_density_all_device": [_vp, _vp, _sz, _sz],
     "eco_fill_density": [_vp, _i32],
+    "eco_fill_density_random": [_vp, _i32, _i32],
     "eco_get_salt": [_vp, _sz, _P(_dbl)],
     "eco_make_consistent": [_vp],
     "eco_seed": [_vp, _u32],

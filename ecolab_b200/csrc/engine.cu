@@ -542,6 +542,29 @@ __global__ void fill_kernel(int32_t* dens, size_t tile_stride, uint32_t ntiles, 
   }
 }
 
+// synthetic initial state: n = lo + draw % span with the stage-3 Philox stream (same contract as the hot path:
+// ctr = {cell, slot>>2, t=0}, key = {seed, 3}); used by benchmarks and full-size property tests
+__global__ void __launch_bounds__(256) fill_random_kernel(int32_t* dens, size_t tile_stride, uint32_t ntiles, uint32_t ntx,
+                                                          uint32_t nx, uint32_t y0, uint32_t nsp, uint32_t seed, int32_t lo,
+                                                          uint32_t span) {
+  const uint32_t lane = threadIdx.x & 31u, wpb = blockDim.x >> 5, ngroups = (nsp + 3) / 4;
+  const unsigned long long nwork = (unsigned long long)ntiles * ngroups;
+  for (unsigned long long w = (unsigned long long)blockIdx.x * wpb + (threadIdx.x >> 5); w < nwork;
+       w += (unsigned long long)gridDim.x * wpb) {
+    const uint32_t g = (uint32_t)(w % ngroups), tile = (uint32_t)(w / ngroups);
+    const uint32_t yl = tile / ntx, tx = tile - yl * ntx, x = tx * 32u + lane;
+    const uint32_t cell = (y0 + yl) * nx + x;
+    const uint4 u = philox4x32_10(cell, g, 0u, 0u, seed, 3u);
+    const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+    int32_t* t = dens + (size_t)tile * tile_stride;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const uint32_t s = 4u * g + r;
+      if (s < nsp) t[s * 32u + lane] = x < nx ? lo + (int32_t)(uu[r] % span) : 0;
+    }
+  }
+}
+
 inline uint32_t round_up4(uint32_t n) { return (n + 3u) & ~3u; }
 
 }  // namespace
@@ -754,6 +777,17 @@ void Engine::fill_density(int32_t v) {
   if (!ntiles || !nsp_) return;
   fill_kernel<<<std::min<unsigned long long>(8192, (unsigned long long)ntiles * nsp_ / 8 + 1), 256, 0, ST>>>(
       row0(cur_), tile_stride(), ntiles, ntx_, nx_, nsp_, v);
+  CK(cudaGetLastError());
+  ++launches_;
+}
+
+void Engine::fill_density_random(uint32_t seed, int32_t lo, int32_t hi) {
+  CK(cudaSetDevice(device_));
+  const uint32_t ntiles = ntx_ * ny_;
+  if (!ntiles || !nsp_) return;
+  const unsigned long long nwork = (unsigned long long)ntiles * ((nsp_ + 3) / 4);
+  fill_random_kernel<<<(unsigned)std::min<unsigned long long>((nwork + 7) / 8, 148ull * 32), 256, 0, ST>>>(
+      row0(cur_), tile_stride(), ntiles, ntx_, nx_, y0_, nsp_, seed, lo, (uint32_t)(hi - lo) + 1u);
   CK(cudaGetLastError());
   ++launches_;
 }

@@ -62,6 +62,7 @@ class Engine {
   void set_density_all_dev(const int32_t* dev, size_t nsp);
   void get_density_all_dev(int32_t* dev, size_t nsp);
   void fill_density(int32_t v);
+  void fill_density_random(uint32_t seed, int32_t lo, int32_t hi);   // lo + philox(stage 3) % (hi-lo+1)
 
   // ---- species data ---------------------------------------------------------
   void upload_beta(const BetaGell& b);

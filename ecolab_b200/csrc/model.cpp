@@ -646,6 +646,14 @@ int eco_fill_density(eco_model* m, int32_t v) {
   m->eng.fill_density(v);
   ECO_CATCH
 }
+int eco_fill_density_random(eco_model* m, int32_t lo, int32_t hi) {
+  ECO_TRY
+  need(m);
+  if (lo < 0 || hi < lo) throw std::runtime_error("fill_density_random: need 0 <= lo <= hi");
+  m->grow_engine(m->nsp());
+  m->eng.fill_density_random(m->seed, lo, hi);
+  ECO_CATCH
+}
 int eco_get_salt(eco_model* m, size_t cell, double* out) {
   ECO_TRY
   need(m);

@@ -227,6 +227,10 @@ class EcolabModelBase:
     def fill_density(self, v):
         check(self._L.eco_fill_density(self._h, int(v)))
 
+    def fill_density_random(self, lo, hi):
+        """n = lo + philox(seed, stage 3, cell, slot, t=0) % (hi-lo+1) on every owned cell (synthetic initial state)."""
+        check(self._L.eco_fill_density_random(self._h, int(lo), int(hi)))
+
     def launches(self):
         return int(self._scalar("launches"))
 

@@ -89,6 +89,9 @@ int eco_get_density_all(eco_model* m, int32_t* out, size_t ncells, size_t nsp);
 int eco_set_density_all_device(eco_model* m, const int32_t* d_dev, size_t ncells, size_t nsp);
 int eco_get_density_all_device(eco_model* m, int32_t* out_dev, size_t ncells, size_t nsp);
 int eco_fill_density(eco_model* m, int32_t value);
+/* synthetic state for benchmarks / full-size property tests (the scripts' `int(100*random())` initialisation,
+ * models/spatial_ecolab.py:44): n[cell][slot] = lo + draw % (hi-lo+1), draw = Philox stage 3 at t=0, current seed */
+int eco_fill_density_random(eco_model* m, int32_t lo, int32_t hi);
 int eco_get_salt(eco_model* m, size_t cell, double* out);   /* EcolabPoint::salt, models/ecolab_model.h:87 */
 
 /* ---- the hot path ----------------------------------------------------------------- */

@@ -675,6 +675,16 @@ void orc_mutate_records(void* h, uint32_t* out) {
   for (size_t i = 0; i < o->pending.size(); ++i) { out[3 * i] = o->pending[i].cell; out[3 * i + 1] = o->pending[i].slot; out[3 * i + 2] = o->pending[i].count; }
 }
 void orc_append_species(void* h, const uint32_t* ids, size_t m) { auto o = (Oracle*)h; o->computeODiagIdx(); o->appendSpecies(ids, m); }
+// synthetic initial state shared with the engine's eco_fill_density_random (Philox stage 3, t = 0)
+void orc_fill_density_random(void* h, int32_t lo, int32_t hi) {
+  auto o = (Oracle*)h;
+  const size_t ns = o->nsp();
+  const uint32_t span = (uint32_t)(hi - lo) + 1u;
+  for (auto& c : o->cells) {
+    c.n.resize(ns);
+    for (size_t s = 0; s < ns; ++s) c.n[s] = lo + (int32_t)(philox_draw(o->seed, 3, c.id, (uint32_t)s, 0) % span);
+  }
+}
 void orc_set_density(void* h, size_t cell, const int32_t* p, size_t n) { ((Oracle*)h)->cells[cell].n.assign(p, p + n); }
 long orc_get_density(void* h, size_t cell, int32_t* p, size_t cap) {
   auto& v = ((Oracle*)h)->cells[cell].n;

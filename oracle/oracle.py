@@ -53,6 +53,7 @@ def lib():
             "orc_get_species": (C.c_long, [vp, vp, sz]),
             "orc_set_grid": (None, [vp, sz, sz]),
             "orc_set_density": (None, [vp, sz, vp, sz]),
+            "orc_fill_density_random": (None, [vp, C.c_int32, C.c_int32]),
             "orc_set_grid_slab": (None, [vp, sz, sz, sz, sz]),
             "orc_migrate_local": (u64, [vp]),
             "orc_set_ghost": (None, [vp, C.c_int, vp, sz]),
@@ -184,6 +185,9 @@ class Oracle:
     def append_species(self, cells):
         a = np.ascontiguousarray(cells, dtype=np.uint32)
         self.L.orc_append_species(self.h, _ptr(a), a.size)
+
+    def fill_density_random(self, lo, hi):
+        self.L.orc_fill_density_random(self.h, lo, hi)
 
     def set_density(self, cell, d):
         a = np.ascontiguousarray(d, dtype=np.int32)

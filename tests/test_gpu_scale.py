@@ -33,8 +33,7 @@ def test_c3_conservation_determinism_and_block_parity(oracle_mod, gpu):
     # block parity: cells of grid row 517, x in [300, 364): ids known, Philox keyed on the global cell id
     y, x0, w = 517, 300, 64
     got = np.array([m.cell(x, y).density() for x in range(x0, x0 + w)], dtype=np.int32)
-    o = load_oracle(oracle_mod, p, np.full((nx * 1, nsp), 100, dtype=np.int32), (nx, 1), seed=10)
-    # an oracle grid of one row has ids 0..nx-1; shift the ids by regenerating with the true ids through the Philox API
+    # restate generate for those cells with the true global ids through the oracle's Philox / ROUND entry points
     O = oracle_mod
     want = np.empty_like(got)
     diag, r = p["interaction.diag"], p["repro_rate"]
@@ -51,14 +50,20 @@ def test_c3_conservation_determinism_and_block_parity(oracle_mod, gpu):
 
     tot0 = m.species_totals()
     moved = m.migrate()
-    assert moved > 0
     assert np.array_equal(m.species_totals(), tot0)       # conservation at full size
-    chk1 = (int(m.species_totals().sum()), moved)
+
+    # uniform 100s barely migrate (|diff|*0.1 < 1 truncates to 0): now a state with gradients
+    m.fill_density_random(0, 199)
+    tot0 = m.species_totals()
+    m.generate(1)
+    tot1 = m.species_totals()
+    moved = m.migrate()
+    assert moved > 10 ** 8 and np.array_equal(m.species_totals(), tot1) and not np.array_equal(tot0, tot1)
 
     m2, _ = build(gpu, nx, ny, nsp, 3)
-    m2.fill_density(100)
+    m2.fill_density_random(0, 199)
     assert m2.step(1) == moved                            # determinism + fused entry point at full size
     assert np.array_equal(m2.species_totals(), m.species_totals())
     a = np.array(m.cell(1023, 1023).density()); b = np.array(m2.cell(1023, 1023).density())
-    assert np.array_equal(a, b) and chk1[0] == int(m2.species_totals().sum())
+    assert np.array_equal(a, b)
     assert min(m.nsp()) > 0
