@@ -162,25 +162,30 @@ def test_mutate_same_streams_bit_exact(oracle_mod, gpu, grid, nsp):
 
 
 def test_mutate_distribution_ks(oracle_mod, gpu):
-    """Statistical equivalence with DIFFERENT random streams (north_star: KS on species counts and traits)."""
+    """Statistical equivalence with DIFFERENT random streams (north_star: KS on species counts and traits).
+    array_grand is a running-CLT generator (src/random.cc:59-64) whose successive values are strongly correlated, so
+    samples are only i.i.d. ACROSS trials: every trial restarts it, and one trait per trial enters the test."""
     from scipy.stats import ks_2samp
     O = oracle_mod
     nsp, grid = 50, (16, 16)
     p = synth(nsp, 3, 12, mut=0.01)
     scal = dict(SCALARS, mut_max=0.01)
     d = densities(256, nsp, 12)
-    counts_o, counts_g, r_o, r_g = [], [], [], []
-    for trial in range(12):
+    counts_o, counts_g, r_o, r_g, mu_o, mu_g = [], [], [], [], [], []
+    for trial in range(60):
         o = load_oracle(O, p, d, grid, seed=1000 + trial, scalars=scal)
         m = load_gpu(gpu, p, d, grid, seed=5000 + trial, scalars=scal)
         o.set("tstep", 10); m.tstep(10)
-        O.srand(trial); o.mutate()
-        O.srand(777 + trial); m.mutate()
+        O.srand(trial); O.reset_grand(); o.mutate()
+        O.srand(7777 + trial); gpu.lib().eco_array_grand_reset(); m.mutate()
         counts_o.append(o.nsp - nsp); counts_g.append(len(m.species) - nsp)
-        r_o += list(o.get("repro_rate")[nsp:]); r_g += list(m.repro_rate()[nsp:])
+        par_o = np.repeat(np.arange(nsp), 0)
+        r_o.append(o.get("repro_rate")[-1]); r_g.append(m.repro_rate()[-1])
+        mu_o.append(o.get("mutation")[-1]); mu_g.append(m.mutation()[-1])
     assert min(counts_o) > 0 and min(counts_g) > 0
     assert ks_2samp(counts_o, counts_g).pvalue > 0.01
     assert ks_2samp(r_o, r_g).pvalue > 0.01
+    assert ks_2samp(mu_o, mu_g).pvalue > 0.01
 
 
 def test_fill_density_random_matches_oracle(oracle_mod, gpu):
