@@ -15,18 +15,15 @@ struct MutRecord {
   uint32_t cell, slot, count;
 };
 
-// beta in "grouped ELL" form: species rows are processed four at a time (one
-// Philox4x32 call yields the four draws of a row group); each group has
-// width = max row length in the group, shorter rows padded with (val 0, col 0).
-// Term order inside a row is the COO order (reference oDiagIdx,
-// models/ecolab_model.cc:718-723) so the FP64 summation order is unchanged.
-struct BetaGell {
-  uint32_t nsp = 0, ngroups = 0;
-  std::vector<uint32_t> gptr;   // [ngroups+1] slot offsets
-  std::vector<double> gval;     // [nslots*4]
-  std::vector<uint32_t> gcol;   // [nslots*4] column * 32 (word offset of the species row in a tile)
-  std::vector<double> diag4;    // [ngroups*4]
-  std::vector<double> rr4;      // [ngroups*4] repro_rate
+// beta in CSR form, rows in species order, the entries of a row in COO order (reference oDiagIdx,
+// models/ecolab_model.cc:718-723) so that the FP64 summation order is the reference's.  The engine
+// re-blocks it into the ELL form its kernels read (k_generate.cuh).
+struct BetaCsr {
+  uint32_t nsp = 0;
+  std::vector<uint32_t> rowptr;   // [nsp+1]
+  std::vector<double> val;        // [nnz]
+  std::vector<uint32_t> col;      // [nnz]
+  std::vector<double> diag, rr;   // [nsp] interaction.diag, repro_rate
 };
 
 class Engine {
@@ -65,7 +62,7 @@ class Engine {
   void fill_density_random(uint32_t seed, int32_t lo, int32_t hi);   // lo + philox(stage 3) % (hi-lo+1)
 
   // ---- species data ---------------------------------------------------------
-  void upload_beta(const BetaGell& b);
+  void upload_beta(const BetaCsr& b);
 
   // ---- hot path -------------------------------------------------------------
   // niter fused Lotka-Volterra steps on every owned cell; t0 = absolute tstep of the first
@@ -90,7 +87,8 @@ class Engine {
   // Device pointers of the boundary rows to send and the ghost rows to receive
   // (each row_bytes() long, contiguous).  Valid until the next migrate()/resize.
   void halo_ptrs(void** send_top, void** send_bottom, void** recv_top, void** recv_bottom);
-  size_t row_bytes() const { return (size_t)ntx_ * cap_ * 32 * sizeof(int32_t); }
+  size_t row_bytes() const { return (size_t)ntx_ * cap_ * tw_ * sizeof(int32_t); }
+  uint32_t tile_width() const { return tw_; }
   // Optional peer pointers (CUDA IPC / P2P): when set, migrate reads the
   // neighbour slabs' boundary rows directly over NVLink instead of ghost rows.
   void set_peer_rows(const void* top_peer_row, const void* bottom_peer_row);
@@ -121,10 +119,13 @@ class Engine {
  private:
   void ensure_other();
   void alloc_buffers(uint32_t cap);
+  void build_ell();
+  void ensure_vec(size_t n);
+  void ensure_mask(size_t n);
   void free_buffers();
   int32_t* row0(int which) const;   // pointer to owned row 0 of buffer `which`
-  size_t tile_stride() const { return (size_t)cap_ * 32; }
-  size_t row_stride() const { return (size_t)ntx_ * cap_ * 32; }
+  size_t tile_stride() const { return (size_t)cap_ * tw_; }
+  size_t row_stride() const { return (size_t)ntx_ * cap_ * tw_; }
 
   int device_ = 0;
   void* stream_ = nullptr;
@@ -133,18 +134,17 @@ class Engine {
   int max_smem_ = 0;
 
   uint32_t nx_ = 1, nyg_ = 1, y0_ = 0, ny_ = 1, ntx_ = 1;
-  uint32_t nsp_ = 0, cap_ = 0;
+  uint32_t nsp_ = 0, cap_ = 0, tw_ = 32;   // live species rows, allocated rows, tile width (cells)
   int32_t* buf_[2] = {nullptr, nullptr};   // allocations (with ghost rows)
   int cur_ = 0;
   const void* peer_top_ = nullptr;
   const void* peer_bottom_ = nullptr;
 
   // beta on device
-  uint32_t ngroups_ = 0;
-  uint32_t* d_gptr_ = nullptr; double* d_gval_ = nullptr; uint32_t* d_gcol_ = nullptr;
-  double* d_diag4_ = nullptr; double* d_rr4_ = nullptr;
-  size_t beta_cap_slots_ = 0, beta_cap_groups_ = 0;
-  uint32_t max_width_ = 0;
+  uint32_t nblocks_ = 0, beta_tw_ = 0, beta_nsp_ = 0;   // ELL blocks; the tile width / species count it was built for
+  uint32_t* d_bptr_ = nullptr; void* d_ell_ = nullptr; void* d_rowpar_ = nullptr;
+  size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_cap_rows_ = 0;
+  BetaCsr beta_host_;                                   // kept to re-block when the tile width changes
 
   // scratch
   double* d_vec_ = nullptr; size_t vec_cap_ = 0;       // per-species doubles (cm / ms)

@@ -37,9 +37,10 @@ struct RunningClt {
   }
 } g_grand;
 
-// host copy of the Philox4x32-10 stream (only for the `salt` getter)
-uint32_t philox_host(uint32_t seed, uint32_t stage, uint32_t cell, uint32_t slot, uint64_t t) {
-  uint32_t c0 = cell, c1 = slot >> 2, c2 = (uint32_t)t, c3 = (uint32_t)(t >> 32), k0 = seed, k1 = stage;
+// host copy of the Philox4x32-10 contract (k_common.cuh), only for the `salt` getter:
+// block = philox(ctr = {(x>>2) | stage<<30, y, slot, t_lo}, key = {seed, t_hi}); draw = block[x & 3]
+uint32_t philox_host(uint32_t seed, uint32_t stage, uint32_t x, uint32_t y, uint32_t slot, uint64_t t) {
+  uint32_t c0 = (x >> 2) | (stage << 30), c1 = y, c2 = slot, c3 = (uint32_t)t, k0 = seed, k1 = (uint32_t)(t >> 32);
   for (int r = 0; r < 10; ++r) {
     const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
     const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
@@ -47,7 +48,7 @@ uint32_t philox_host(uint32_t seed, uint32_t stage, uint32_t cell, uint32_t slot
     k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
   }
   const uint32_t o[4] = {c0, c1, c2, c3};
-  return o[slot & 3];
+  return o[x & 3];
 }
 
 void add_noise(std::vector<double>& a, const std::vector<double>& scale) {          // gspread, src/arrays.cc:94-100
@@ -126,42 +127,28 @@ struct eco_model {
       throw std::runtime_error("inconsistent model: interaction.row/col/val differ in length");
   }
 
-  // build the grouped-ELL form of beta; term order inside a row = COO order (oDiagIdx, :718-723)
+  // hand beta to the engine as CSR; term order inside a row = COO order (computeODiagIdx, :718-723)
   void upload() {
     if (!beta_dirty) return;
     const uint32_t n = (uint32_t)nsp();
-    std::vector<uint32_t> cnt(n + 1, 0);
+    eco::BetaCsr b;
+    b.nsp = n;
+    b.rowptr.assign(n + 1, 0);
     for (size_t j = 0; j < row.size(); ++j) {
       if (row[j] >= n || col[j] >= n) throw std::runtime_error("interaction.row/col index out of range");
-      ++cnt[row[j] + 1];
+      ++b.rowptr[row[j] + 1];
     }
-    for (uint32_t i = 0; i < n; ++i) cnt[i + 1] += cnt[i];
-    std::vector<uint32_t> order(row.size()), pos(cnt.begin(), cnt.end() - 1);
-    for (size_t j = 0; j < row.size(); ++j) order[pos[row[j]]++] = (uint32_t)j;   // stable: ascending j inside a row
-    eco::BetaGell b;
-    b.nsp = n;
-    b.ngroups = (n + 3) / 4;
-    b.gptr.assign(b.ngroups + 1, 0);
-    for (uint32_t g = 0; g < b.ngroups; ++g) {
-      uint32_t w = 0;
-      for (uint32_t r = 0; r < 4 && 4 * g + r < n; ++r) w = std::max(w, cnt[4 * g + r + 1] - cnt[4 * g + r]);
-      b.gptr[g + 1] = b.gptr[g] + w;
+    for (uint32_t i = 0; i < n; ++i) b.rowptr[i + 1] += b.rowptr[i];
+    std::vector<uint32_t> pos(b.rowptr.begin(), b.rowptr.end() - 1);
+    b.val.resize(row.size());
+    b.col.resize(row.size());
+    for (size_t j = 0; j < row.size(); ++j) {   // stable: ascending j inside a row
+      const uint32_t k = pos[row[j]]++;
+      b.val[k] = val[j];
+      b.col[k] = col[j];
     }
-    const size_t nslots = b.gptr[b.ngroups];
-    b.gval.assign(nslots * 4, 0.0);
-    b.gcol.assign(nslots * 4, 0u);
-    b.diag4.assign((size_t)b.ngroups * 4, 0.0);
-    b.rr4.assign((size_t)b.ngroups * 4, 0.0);
-    for (uint32_t i = 0; i < n; ++i) {
-      const uint32_t g = i / 4, r = i % 4;
-      b.diag4[i] = diag[i];
-      b.rr4[i] = repro_rate[i];
-      for (uint32_t k = cnt[i]; k < cnt[i + 1]; ++k) {
-        const size_t slot = (size_t)b.gptr[g] + (k - cnt[i]);
-        b.gval[slot * 4 + r] = val[order[k]];
-        b.gcol[slot * 4 + r] = col[order[k]] * 32u;
-      }
-    }
+    b.diag = diag;
+    b.rr = repro_rate;
     eng.upload_beta(b);
     beta_dirty = false;
   }
@@ -657,7 +644,7 @@ int eco_fill_density_random(eco_model* m, int32_t lo, int32_t hi) {
 int eco_get_salt(eco_model* m, size_t cell, double* out) {
   ECO_TRY
   need(m);
-  *out = (double)philox_host(m->seed, 2, (uint32_t)cell, 0, m->salt_t) / 4294967295.0;   // :619-620
+  *out = (double)philox_host(m->seed, 2, (uint32_t)(cell % m->numX), (uint32_t)(cell / m->numX), 0, m->salt_t) / 4294967295.0;   // :619-620
   ECO_CATCH
 }
 

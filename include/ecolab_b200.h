@@ -20,8 +20,9 @@
  *     thread per handle (the reference is driven under the GIL).
  *   - the engine requires a CUDA device: eco_create fails loudly without one.
  *     There is no CPU fallback.
- *   - RNG: counter-based Philox4x32-10, ctr={cell id, slot>>2, t_lo, t_hi},
- *     key={seed, stage}, stage 0=generate 1=mutate 2=salt.
+ *   - RNG: counter-based Philox4x32-10; for cell (x, y), species slot s, timestep t:
+ *     block = philox(ctr={(x>>2) | stage<<30, y, s, t_lo}, key={seed, t_hi}), draw = block[x & 3];
+ *     stage 0=generate 1=mutate 2=salt 3=synthetic fill (DESIGN.md "RNG contract").
  */
 #ifndef ECOLAB_B200_H
 #define ECOLAB_B200_H

@@ -26,9 +26,9 @@
 //   MT19937 : one std::mt19937 per cell, consumed sequentially exactly as the
 //             reference does (models/ecolab_model.h:97-102).
 //   PHILOX  : counter-based Philox4x32-10, the stream shared with the GPU
-//             (contract in DESIGN.md section "RNG contract"):
-//               ctr = {cell id, slot>>2, t_lo, t_hi}, key = {seed, stage}
-//               draw = out[slot & 3]
+//             (contract in DESIGN.md section "RNG contract"), cell (x, y) = (id % numX, id / numX):
+//               ctr = {(x>>2) | stage<<30, y, slot, t_lo}, key = {seed, t_hi}
+//               draw = out[x & 3]
 //
 // Build: g++ -O3 -fopenmp -ffp-contract=off (the reference builds x86-64
 // without FMA, include/Makefile:567-571); see oracle/Makefile.
@@ -64,15 +64,19 @@ inline void philox_round(uint32_t c[4], const uint32_t k[2]) {
   const uint32_t n3 = (uint32_t)p0;
   c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
 }
-inline uint32_t philox_draw(uint32_t seed, uint32_t stage, uint32_t cell,
-                            uint32_t slot, uint64_t t) {
-  uint32_t c[4] = {cell, slot >> 2, (uint32_t)t, (uint32_t)(t >> 32)};
-  uint32_t k[2] = {seed, stage};
+inline void philox_block(uint32_t c[4], uint32_t k0, uint32_t k1) {
+  uint32_t k[2] = {k0, k1};
   for (int r = 0; r < 10; ++r) {
     if (r) { k[0] += 0x9E3779B9u; k[1] += 0xBB67AE85u; }
     philox_round(c, k);
   }
-  return c[slot & 3];
+}
+// the shared stream: one block serves the 4 consecutive cells x&~3 .. x|3 of grid row y for one species slot
+inline uint32_t philox_draw(uint32_t seed, uint32_t stage, uint32_t x, uint32_t y,
+                            uint32_t slot, uint64_t t) {
+  uint32_t c[4] = {(x >> 2) | (stage << 30), y, slot, (uint32_t)t};
+  philox_block(c, seed, (uint32_t)(t >> 32));
+  return c[x & 3];
 }
 
 // ---- libc-rand() based generators used by ModelData::mutate --------------------
@@ -129,7 +133,7 @@ struct Oracle {
 
   uint32_t draw(Cell& c, uint32_t stage, uint32_t slot, uint64_t t) {
     if (rng_mode == RNG_MT19937) return (uint32_t)c.mt();
-    return philox_draw(seed, stage, c.id, slot, t);
+    return philox_draw(seed, stage, (uint32_t)(c.id % numX), (uint32_t)(c.id / numX), slot, t);
   }
 
   // models/ecolab_model.cc:57-66  EcolabPoint::ROUND
@@ -682,7 +686,7 @@ void orc_fill_density_random(void* h, int32_t lo, int32_t hi) {
   const uint32_t span = (uint32_t)(hi - lo) + 1u;
   for (auto& c : o->cells) {
     c.n.resize(ns);
-    for (size_t s = 0; s < ns; ++s) c.n[s] = lo + (int32_t)(philox_draw(o->seed, 3, c.id, (uint32_t)s, 0) % span);
+    for (size_t s = 0; s < ns; ++s) c.n[s] = lo + (int32_t)(philox_draw(o->seed, 3, (uint32_t)(c.id % o->numX), (uint32_t)(c.id / o->numX), (uint32_t)s, 0) % span);
   }
 }
 void orc_set_density(void* h, size_t cell, const int32_t* p, size_t n) { ((Oracle*)h)->cells[cell].n.assign(p, p + n); }
@@ -728,8 +732,13 @@ long orc_get_pre(void* h, double* p, size_t cap) {
   if (p) std::copy(v.begin(), v.begin() + std::min(cap, v.size()), p);
   return (long)v.size();
 }
-uint32_t orc_philox(uint32_t seed, uint32_t stage, uint32_t cell, uint32_t slot, uint64_t t) {
-  return philox_draw(seed, stage, cell, slot, t);
+uint32_t orc_philox(uint32_t seed, uint32_t stage, uint32_t x, uint32_t y, uint32_t slot, uint64_t t) {
+  return philox_draw(seed, stage, x, y, slot, t);
+}
+void orc_philox_raw(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {   // known-answer tests
+  uint32_t c[4] = {ctr[0], ctr[1], ctr[2], ctr[3]};
+  philox_block(c, key[0], key[1]);
+  for (int i = 0; i < 4; ++i) out[i] = c[i];
 }
 int orc_round(double x, uint32_t u) {   // ROUND with an injected draw (unit tests)
   const Float maxInt = Float(INT_MAX - 1);

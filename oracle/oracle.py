@@ -77,7 +77,8 @@ def lib():
             "orc_lifetimes": (C.c_long, [vp, vp, sz]),
             "orc_nsp_per_cell": (None, [vp, vp]),
             "orc_get_pre": (C.c_long, [vp, vp, sz]),
-            "orc_philox": (u32, [u32, u32, u32, u32, u64]),
+            "orc_philox": (u32, [u32, u32, u32, u32, u32, u64]),
+            "orc_philox_raw": (None, [vp, vp, vp]),
             "orc_round": (C.c_int, [dbl, u32]),
         }
         for name, (res, args) in sig.items():
@@ -259,8 +260,16 @@ class Oracle:
         return a
 
 
-def philox(seed, stage, cell, slot, t):
-    return int(lib().orc_philox(seed, stage, cell, slot, t))
+def philox(seed, stage, x, y, slot, t):
+    """The shared stream's draw for cell (x, y), species slot `slot`, timestep t."""
+    return int(lib().orc_philox(seed, stage, x, y, slot, t))
+
+
+def philox_raw(ctr, key):
+    """Plain Philox4x32-10 block (known-answer tests against the Random123 vectors)."""
+    c = np.array(ctr, dtype=np.uint32); k = np.array(key, dtype=np.uint32); o = np.zeros(4, dtype=np.uint32)
+    lib().orc_philox_raw(_ptr(c), _ptr(k), _ptr(o))
+    return [int(v) for v in o]
 
 
 def round_with_draw(x, u):

@@ -179,7 +179,6 @@ def test_mutate_distribution_ks(oracle_mod, gpu):
         O.srand(trial); O.reset_grand(); o.mutate()
         O.srand(7777 + trial); gpu.lib().eco_array_grand_reset(); m.mutate()
         counts_o.append(o.nsp - nsp); counts_g.append(len(m.species) - nsp)
-        par_o = np.repeat(np.arange(nsp), 0)
         r_o.append(o.get("repro_rate")[-1]); r_g.append(m.repro_rate()[-1])
         mu_o.append(o.get("mutation")[-1]); mu_g.append(m.mutation()[-1])
     assert min(counts_o) > 0 and min(counts_g) > 0

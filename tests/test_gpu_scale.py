@@ -44,8 +44,7 @@ def test_c3_conservation_determinism_and_block_parity(oracle_mod, gpu):
         ir[row[j]] = ir[row[j]] + val[j] * 100.0
     x = 100.0 + 100.0 * (r + ir)
     for i in range(w):
-        cid = (x0 + i) + nx * y
-        want[i] = [O.round_with_draw(x[s], O.philox(10, 0, cid, s, 0)) for s in range(nsp)]
+        want[i] = [O.round_with_draw(x[s], O.philox(10, 0, x0 + i, y, s, 0)) for s in range(nsp)]
     assert np.array_equal(got, want)
 
     tot0 = m.species_totals()

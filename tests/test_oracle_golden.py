@@ -170,13 +170,20 @@ def test_round_edges(oracle_mod):
 
 
 def test_philox_known_answer(oracle_mod):
-    # Random123 kat_vectors: philox4x32-10, counter = key = 0
+    # Random123 kat_vectors, philox4x32-10
     O = oracle_mod
-    assert [O.philox(0, 0, 0, s, 0) for s in range(4)] == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
-    # a draw depends on every field of the contract ctr={cell, slot>>2, t_lo, t_hi}, key={seed, stage}
-    base = O.philox(1, 0, 2, 4, 3)
-    assert len({base, O.philox(2, 0, 2, 4, 3), O.philox(1, 1, 2, 4, 3), O.philox(1, 0, 3, 4, 3), O.philox(1, 0, 2, 8, 3),
-                O.philox(1, 0, 2, 4, 4), O.philox(1, 0, 2, 4, 3 + (1 << 32)), O.philox(1, 0, 2, 5, 3)}) == 8
+    assert O.philox_raw([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert O.philox_raw([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert O.philox_raw([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    # the contract: ctr = {(x>>2) | stage<<30, y, slot, t_lo}, key = {seed, t_hi}, draw = block[x & 3]
+    blk = O.philox_raw([(9 >> 2) | (1 << 30), 7, 5, 3], [11, 2])
+    assert O.philox(11, 1, 9, 7, 5, 3 + (2 << 32)) == blk[9 & 3]
+    assert [O.philox(11, 1, x, 7, 5, 3 + (2 << 32)) for x in (8, 9, 10, 11)] == blk
+    base = O.philox(1, 0, 2, 6, 4, 3)
+    assert len({base, O.philox(2, 0, 2, 6, 4, 3), O.philox(1, 1, 2, 6, 4, 3), O.philox(1, 0, 3, 6, 4, 3), O.philox(1, 0, 6, 6, 4, 3),
+                O.philox(1, 0, 2, 7, 4, 3), O.philox(1, 0, 2, 6, 5, 3), O.philox(1, 0, 2, 6, 4, 4),
+                O.philox(1, 0, 2, 6, 4, 3 + (1 << 32))}) == 9
 
 
 def test_committed_golden_fixtures(oracle_mod):
