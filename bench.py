@@ -167,6 +167,10 @@ def build_model(E, args, nx, ny, comm, device, stream):
             getattr(m, k)(v)
     m.setGrid(nx, ny)
     m.seed(10)
+    for knob, val in (("gen_threads", args.gen_warps), ("gen_stages", args.gen_stages), ("gen_nofma", args.gen_nofma),
+                      ("mig_variant", args.mig_variant)):
+        if val:
+            m.set_tuning(knob, val)
     m.fill_density_random(0, 199)   # mean 100, with gradients between neighbours so migrate really moves population
     return m
 
@@ -322,6 +326,10 @@ def main():
     ap.add_argument("--nsp", type=int, default=1024)
     ap.add_argument("--nnz", type=int, default=3)
     ap.add_argument("--e2e-n", type=int, default=1024, dest="e2e_n")
+    ap.add_argument("--gen-warps", type=int, default=0, dest="gen_warps")
+    ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
+    ap.add_argument("--gen-nofma", type=int, default=0, dest="gen_nofma")
+    ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

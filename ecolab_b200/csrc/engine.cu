@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -36,13 +37,13 @@ namespace {
 constexpr size_t kSmemPerSm = 227 * 1024;
 inline uint32_t round_up32(uint32_t n) { return (n + 31u) & ~31u; }
 
-// Tile width for a species capacity: the widest tile of which three fit in one SM's shared memory
-// (three resident generate CTAs hide each other's bulk loads); failing that the widest that fits once.
+// Tile width for a species capacity: the widest tile of which two fit the generate pipeline's 128 KB ring
+// (the rest of the SM's 256 KB stays L1 and holds beta); failing that the widest that fits the SM twice, then once.
 uint32_t pick_tile_width(uint32_t cap) {
   for (uint32_t tw : {32u, 16u, 8u, 4u})
-    if (3 * ((size_t)cap * tw * 4 + 1024) <= kSmemPerSm) return tw;
-  for (uint32_t tw : {16u, 8u, 4u})
-    if ((size_t)cap * tw * 4 + 1024 <= kSmemPerSm) return tw;
+    if (2 * (size_t)cap * tw * 4 <= 128 * 1024) return tw;
+  if (2 * ((size_t)cap * 16 + 64) + (size_t)cap + 1024 <= kSmemPerSm) return 4;
+  if ((size_t)cap * 16 + (size_t)cap + 1024 <= kSmemPerSm) return 4;
   throw std::runtime_error("species count exceeds the shared-memory tile (nsp*16 B must fit in 227 KB)");
 }
 
@@ -73,7 +74,7 @@ Engine::~Engine() {
   cudaSetDevice(device_);
   cudaDeviceSynchronize();
   free_buffers();
-  cudaFree(d_bptr_); cudaFree(d_ell_); cudaFree(d_rowpar_);
+  cudaFree(d_boff_); cudaFree(d_stream_);
   cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_stage_);
   cudaFreeHost(h_total_);
   if (ev_total_) cudaEventDestroy((cudaEvent_t)ev_total_);

@@ -81,6 +81,15 @@ __device__ __forceinline__ int round_stoch(double x, uint32_t u) {
   return r;
 }
 
+// the same for 0 <= x < 2^31-256 (callers check the range on x's high word): both clamps are no-ops there.
+// x = +0 gives trunc 0, frac 0, ceil(0) = 0 > u false -> 0, as the reference's x<=0 branch.
+__device__ __forceinline__ int round_stoch_inrange(double x, uint32_t u) {
+  const double t = __dadd_rz(x, TWO52);
+  const double f = __dadd_rn(x, -__dadd_rn(t, -TWO52));
+  const uint32_t cp = (uint32_t)__double2loint(__dadd_ru(__dmul_rn(f, 4294967295.0), TWO52));
+  return __double2loint(t) + (cp > u ? 1 : 0);
+}
+
 // ---- mbarrier / bulk-copy (TMA unit) wrappers ------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -88,6 +97,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(

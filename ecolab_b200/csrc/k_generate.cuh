@@ -1,13 +1,23 @@
 // k_generate.cuh -- the generalised Lotka-Volterra step with stochastic rounding
 // (reference EcolabPoint::generate, models/ecolab_model.cc:90-112; ROUND :57-66).
 //
-// beta on the device is a blocked ELL matrix matched to the lane map: species rows are processed
-// ROWS = 128/TW at a time (one warp-op); block b has width = longest row in the block, shorter rows
-// padded with (val 0, offset 0).  Entry (slot j, row r) is the 16-byte record
-//     { double val ; uint32 byte offset of species row `col` inside a tile ; pad }
-// at ell[j*ROWS + r], so the lanes of one row fetch one broadcast 16-byte load per term.  Terms of a
-// row keep the COO order (reference oDiagIdx, :718-723) so the FP64 summation order is the reference's:
-//     ir = diag*n ; ir += val_j * n[col_j] (j ascending) ; x = n + n*(r + ir), every op individually rounded.
+// beta on the device is a blocked-ELL *stream* matched to the lane map.  Species rows are processed
+// ROWS = 128/TW at a time (one warp-op: ROWS rows x TW cells, a lane owns 4 consecutive cells of one row).
+// Block b occupies the 16-byte records  stream[boff[b]*ROWS ... boff[b+1]*ROWS):
+//     slot 0      : ROWS headers  { double diag ; double repro_rate }
+//     slot 1..W_b : ROWS terms    { val.lo, val.hi, byte offset of species row `col` inside a tile, hi word of c }
+// where W_b = longest row of the block (shorter rows are padded with val = 0, c = 0, offset 0) and
+// c = -val * 2^52, whose low word equals val's (exact power-of-two scaling), so only its high word is stored.
+// A warp-op therefore reads its whole beta block through ONE base pointer with immediate offsets.
+// Terms of a row keep the COO order (reference oDiagIdx, :718-723) so the FP64 summation order is the reference's:
+//     ir = diag*n ; ir = ir + val_j*n[col_j] (j ascending) ; x = n + n*(r + ir), every operation individually rounded.
+//
+// The product val*n is formed as fma(val, 2^52 + n, -val*2^52): the fused operation rounds the EXACT value
+// val*(2^52+n) - val*2^52 = val*n once, i.e. it returns RN(val*n) -- bit-identical to the reference's separate
+// multiply -- while the int->double conversion of n costs nothing (2^52+n is the int paired with a constant high
+// word).  This removes one FP64-pipe instruction per term and cell; the accumulate stays a separate add.
+// The host only selects this path when every val is a normal double of moderate magnitude (FMAPROD), else the
+// kernel converts n explicitly and multiplies (same results, one more FP64 instruction per term).
 #pragma once
 #include "k_common.cuh"
 
@@ -16,60 +26,164 @@ namespace eco {
 struct GenParams {
   Layout L;
   uint32_t nblocks;          // ceil(nsp / ROWS)
-  const uint32_t* bptr;      // [nblocks+1] slot offsets
-  const uint4* ell;          // [nslots*ROWS]
-  const double2* rowpar;     // [nblocks*ROWS] {diag, repro_rate}
+  const uint32_t* boff;      // [nblocks+1] slot offsets of the blocks inside `stream`
+  const uint4* stream;       // beta stream, see above
   uint32_t seed, niter;
   unsigned long long t0;
+  uint32_t nstages;          // pipeline kernel: shared-memory tile buffers
 };
 
-// One warp-op: ROWS species rows x TW cells; this lane owns 4 consecutive cells of one row.
-// `lp` = shared-memory tile + 4*quad (ints); returns the four pre-rounding values.
-template <int TW>
-__device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, uint32_t row, uint32_t rr, uint32_t b,
-                                      const GenParams& p, double x[4]) {
+__device__ __forceinline__ double dbl(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
+__device__ __forceinline__ double bigu(int n) { return __hiloint2double(0x43300000, n); }   // 2^52 + n, 0 <= n < 2^32
+
+// One warp-op: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of species row `row`.
+// `lp` = shared-memory tile + 4*quad (ints); `blk` = this lane's header record of block b; W = terms per row.
+template <int TW, bool FMAPROD>
+__device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, uint32_t row, const uint4* __restrict__ blk,
+                                      uint32_t W, double x[4]) {
   constexpr int R = LaneMap<TW>::ROWS;
   const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
-  const double d0 = u2d((uint32_t)own.x), d1 = u2d((uint32_t)own.y), d2 = u2d((uint32_t)own.z), d3 = u2d((uint32_t)own.w);
-  const double2 par = __ldg(p.rowpar + row);
-  double ir0 = __dmul_rn(par.x, d0), ir1 = __dmul_rn(par.x, d1), ir2 = __dmul_rn(par.x, d2), ir3 = __dmul_rn(par.x, d3);
-  uint32_t j = __ldg(p.bptr + b);
-  const uint32_t je = __ldg(p.bptr + b + 1);
-  const uint4* e = p.ell + (size_t)j * R + rr;
-  for (; j < je; ++j, e += R) {
+  const uint4 h = __ldg(blk);
+  const double diag = dbl(h.x, h.y), rr = dbl(h.z, h.w);
+  const double d0 = (double)(uint32_t)own.x, d1 = (double)(uint32_t)own.y, d2 = (double)(uint32_t)own.z,
+               d3 = (double)(uint32_t)own.w;
+  double ir0 = __dmul_rn(diag, d0), ir1 = __dmul_rn(diag, d1), ir2 = __dmul_rn(diag, d2), ir3 = __dmul_rn(diag, d3);
+  const uint4* e = blk + R;
+#pragma unroll 4
+  for (uint32_t j = 0; j < W; ++j, e += R) {
     const uint4 w = __ldg(e);
-    const double v = __hiloint2double((int)w.y, (int)w.x);
+    const double v = dbl(w.x, w.y);
     const int4 g = *reinterpret_cast<const int4*>(reinterpret_cast<const char*>(lp) + w.z);
-    ir0 = __dadd_rn(ir0, __dmul_rn(v, u2d((uint32_t)g.x)));
-    ir1 = __dadd_rn(ir1, __dmul_rn(v, u2d((uint32_t)g.y)));
-    ir2 = __dadd_rn(ir2, __dmul_rn(v, u2d((uint32_t)g.z)));
-    ir3 = __dadd_rn(ir3, __dmul_rn(v, u2d((uint32_t)g.w)));
+    if (FMAPROD) {
+      const double c = dbl(w.x, w.w);
+      ir0 = __dadd_rn(ir0, __fma_rn(v, bigu(g.x), c));
+      ir1 = __dadd_rn(ir1, __fma_rn(v, bigu(g.y), c));
+      ir2 = __dadd_rn(ir2, __fma_rn(v, bigu(g.z), c));
+      ir3 = __dadd_rn(ir3, __fma_rn(v, bigu(g.w), c));
+    } else {
+      ir0 = __dadd_rn(ir0, __dmul_rn(v, (double)(uint32_t)g.x));
+      ir1 = __dadd_rn(ir1, __dmul_rn(v, (double)(uint32_t)g.y));
+      ir2 = __dadd_rn(ir2, __dmul_rn(v, (double)(uint32_t)g.z));
+      ir3 = __dadd_rn(ir3, __dmul_rn(v, (double)(uint32_t)g.w));
+    }
   }
-  x[0] = __dadd_rn(d0, __dmul_rn(d0, __dadd_rn(par.y, ir0)));
-  x[1] = __dadd_rn(d1, __dmul_rn(d1, __dadd_rn(par.y, ir1)));
-  x[2] = __dadd_rn(d2, __dmul_rn(d2, __dadd_rn(par.y, ir2)));
-  x[3] = __dadd_rn(d3, __dmul_rn(d3, __dadd_rn(par.y, ir3)));
+  x[0] = __dadd_rn(d0, __dmul_rn(d0, __dadd_rn(rr, ir0)));
+  x[1] = __dadd_rn(d1, __dmul_rn(d1, __dadd_rn(rr, ir1)));
+  x[2] = __dadd_rn(d2, __dmul_rn(d2, __dadd_rn(rr, ir2)));
+  x[3] = __dadd_rn(d3, __dmul_rn(d3, __dadd_rn(rr, ir3)));
 }
 
-// Persistent CTAs; each iteration: bulk-copy one tile (all species of TW cells) into shared memory, run
-// `niter` Jacobi steps, write the tile back in place.
-//  DB=false: niter==1, one smem buffer, results stored straight to HBM as 16-byte vectors (a warp-op
-//            writes 512 contiguous bytes); several CTAs are resident per SM so one CTA's bulk load
-//            overlaps the others' arithmetic.
-//  DB=true : two smem buffers, any niter (HBM traffic amortised over niter).
-template <int TW, int THREADS, int MINB, bool DB>
-__global__ void __launch_bounds__(THREADS, MINB) generate_kernel(const GenParams p) {
+// ROUND of the lane's four values.  Fast path: 0 <= x < 2^31-256 for all four (decided on the high words with
+// integer compares, one warp-uniform branch); otherwise the fully guarded round_stoch.
+__device__ __forceinline__ int4 round4(const double x[4], const uint4 u) {
+  const uint32_t h0 = (uint32_t)__double2hiint(x[0]), h1 = (uint32_t)__double2hiint(x[1]),
+                 h2 = (uint32_t)__double2hiint(x[2]), h3 = (uint32_t)__double2hiint(x[3]);
+  const uint32_t hm = max(max(h0, h1), max(h2, h3));     // negative x has the sign bit set -> huge as unsigned
+  int4 o;
+  if (__any_sync(FULL, hm >= 0x41DFFFFFu)) {
+    o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
+    o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
+  } else {
+    o.x = round_stoch_inrange(x[0], u.x); o.y = round_stoch_inrange(x[1], u.y);
+    o.z = round_stoch_inrange(x[2], u.z); o.w = round_stoch_inrange(x[3], u.w);
+  }
+  return o;
+}
+
+__device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t* src, uint32_t tile_bytes, uint64_t* bar) {
+  mbar_expect_tx(bar, tile_bytes);
+  for (uint32_t off = 0; off < tile_bytes; off += 32768u) {   // modest requests, one barrier
+    const uint32_t n = min(32768u, tile_bytes - off);
+    bulk_g2s(reinterpret_cast<unsigned char*>(dst_smem) + off, reinterpret_cast<const unsigned char*>(src) + off, n, bar);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// generate(1): persistent producer/consumer pipeline, one CTA per SM.
+//   warp NW        : producer -- one lane streams the CTA's tiles (all species of TW cells, one contiguous
+//                    block in HBM) into a ring of `nstages` shared-memory buffers with bulk (TMA-unit) copies,
+//                    completion on per-stage "full" mbarriers; it re-fills a buffer as soon as all consumer
+//                    warps have arrived on its "empty" mbarrier.
+//   warps 0..NW-1  : consumers -- warp-ops (ROWS species rows x TW cells) are dealt round-robin over the warps
+//                    across tile boundaries, so the load stays balanced when nblocks is not a multiple of NW and
+//                    no CTA-wide barrier exists: a warp that is done with a tile moves on to the next one.
+// Results go straight from registers to HBM as 16-byte vectors (a warp-op writes 512 contiguous bytes), in place.
+// ---------------------------------------------------------------------------------------------------------
+template <int TW, int NW, bool FMAPROD>
+__global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
-  const uint32_t rows = p.nblocks * R;
-  const uint32_t tile_words = rows * TW;
-  const uint32_t tile_bytes = tile_words * 4u;
+  const uint32_t nblocks = p.nblocks, S = p.nstages;
+  const uint32_t tile_words = nblocks * R * TW, tile_bytes = tile_words * 4u;
+  int32_t* tiles = reinterpret_cast<int32_t*>(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)S * tile_bytes);
+  uint64_t* empty = full + S;
+  uint32_t* s_boff = reinterpret_cast<uint32_t*>(empty + S);
+
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (uint32_t i = threadIdx.x; i <= nblocks; i += (NW + 1) * 32) s_boff[i] = p.boff[i];
+  if (threadIdx.x == 0) {
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, NW); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const uint32_t ntiles = p.L.ntx * p.L.ny;
+  if (warp == NW) {
+    if (lane == 0) {
+      uint32_t stage = 0, round = 0;
+      for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
+        if (round) mbar_wait(empty + stage, (round - 1u) & 1u);
+        load_tile_bulk(tiles + (size_t)stage * tile_words, p.L.base + (size_t)tile_id * p.L.tile_stride, tile_bytes, full + stage);
+        if (++stage == S) { stage = 0; ++round; }
+      }
+    }
+    return;
+  }
+
+  const uint32_t rr = LaneMap<TW>::row(lane), q = LaneMap<TW>::quad(lane);
+  const uint32_t nbm = nblocks % NW;
+  uint32_t first = warp, stage = 0, round = 0;
+  for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
+    mbar_wait(full + stage, round & 1u);
+    const int32_t* lp = tiles + (size_t)stage * tile_words + 4 * q;
+    int32_t* gl = p.L.base + (size_t)tile_id * p.L.tile_stride + 4 * q;
+    const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
+    const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
+    for (uint32_t b = first; b < nblocks; b += NW) {
+      const uint32_t row = b * R + rr;
+      const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
+      double x[4];
+      gen_x<TW, FMAPROD>(lp, row, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+      const int4 o = round4(x, draw4(xq, yg, row, p.t0, p.seed, 0u));
+      __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
+    }
+    first += NW - nbm;
+    if (first >= NW) first -= NW;
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + stage);
+    if (++stage == S) { stage = 0; ++round; }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// generate(niter > 1): per tile, `niter` Jacobi steps between two shared-memory buffers (HBM traffic amortised
+// over niter -- the scripts' cadence is generate(100), models/spatial_ecolab.py:67), CTA-wide barrier per step.
+// ---------------------------------------------------------------------------------------------------------
+template <int TW, int THREADS, bool FMAPROD>
+__global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int R = LaneMap<TW>::ROWS;
+  const uint32_t nblocks = p.nblocks;
+  const uint32_t tile_words = nblocks * R * TW, tile_bytes = tile_words * 4u;
   int32_t* buf0 = reinterpret_cast<int32_t*>(smem_raw);
-  int32_t* buf1 = buf0 + (DB ? tile_words : 0);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + (size_t)tile_bytes * (DB ? 2 : 1));
+  int32_t* buf1 = buf0 + tile_words;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + (size_t)tile_bytes * 2);
+  uint32_t* s_boff = reinterpret_cast<uint32_t*>(bar + 1);
 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = THREADS / 32;
   const uint32_t rr = LaneMap<TW>::row(lane), q = LaneMap<TW>::quad(lane);
+  for (uint32_t i = threadIdx.x; i <= nblocks; i += THREADS) s_boff[i] = p.boff[i];
   if (threadIdx.x == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -81,63 +195,42 @@ __global__ void __launch_bounds__(THREADS, MINB) generate_kernel(const GenParams
   for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
     int32_t* gt = p.L.base + (size_t)tile_id * p.L.tile_stride;
     if (threadIdx.x == 0) {
-      mbar_expect_tx(bar, tile_bytes);
-      for (uint32_t off = 0; off < tile_bytes; off += 32768u) {   // modest requests, one barrier
-        const uint32_t n = min(32768u, tile_bytes - off);
-        bulk_g2s(reinterpret_cast<unsigned char*>(buf0) + off, reinterpret_cast<const unsigned char*>(gt) + off, n, bar);
-      }
+      load_tile_bulk(buf0, gt, tile_bytes, bar);
       const uint32_t nxt = tile_id + gridDim.x;
       if (nxt < ntiles) bulk_prefetch_l2(p.L.base + (size_t)nxt * p.L.tile_stride, tile_bytes);
     }
     mbar_wait(bar, phase);
     phase ^= 1u;
-
     const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
     const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
-
-    if (!DB) {
-      const int32_t* lp = buf0 + 4 * q;
-      for (uint32_t b = warp; b < p.nblocks; b += nwarps) {
+    int32_t* src = buf0;
+    int32_t* dst = buf1;
+    for (uint32_t step = 0; step < p.niter; ++step) {
+      const int32_t* lp = src + 4 * q;
+      for (uint32_t b = warp; b < nblocks; b += nwarps) {
         const uint32_t row = b * R + rr;
+        const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
         double x[4];
-        gen_x<TW>(lp, row, rr, b, p, x);
-        const uint4 u = draw4(xq, yg, row, p.t0, p.seed, 0u);
-        int4 o;
-        o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
-        o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
-        *reinterpret_cast<int4*>(gt + row * TW + 4 * q) = o;
+        gen_x<TW, FMAPROD>(lp, row, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+        const int4 o = round4(x, draw4(xq, yg, row, p.t0 + step, p.seed, 0u));
+        *reinterpret_cast<int4*>(dst + row * TW + 4 * q) = o;
       }
-      __syncthreads();   // everyone done reading buf0 before the next bulk copy lands
-    } else {
-      int32_t* src = buf0;
-      int32_t* dst = buf1;
-      for (uint32_t step = 0; step < p.niter; ++step) {
-        const int32_t* lp = src + 4 * q;
-        for (uint32_t b = warp; b < p.nblocks; b += nwarps) {
-          const uint32_t row = b * R + rr;
-          double x[4];
-          gen_x<TW>(lp, row, rr, b, p, x);
-          const uint4 u = draw4(xq, yg, row, p.t0 + step, p.seed, 0u);
-          int4 o;
-          o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
-          o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
-          *reinterpret_cast<int4*>(dst + row * TW + 4 * q) = o;
-        }
-        __syncthreads();
-        int32_t* tmp = src; src = dst; dst = tmp;
-      }
-      const int4* s4 = reinterpret_cast<const int4*>(src);
-      int4* g4 = reinterpret_cast<int4*>(gt);
-      for (uint32_t i = threadIdx.x; i < tile_words / 4; i += THREADS) g4[i] = s4[i];
       __syncthreads();
+      int32_t* tmp = src; src = dst; dst = tmp;
     }
+    const int4* s4 = reinterpret_cast<const int4*>(src);
+    int4* g4 = reinterpret_cast<int4*>(gt);
+    for (uint32_t i = threadIdx.x; i < tile_words / 4; i += THREADS) g4[i] = s4[i];
+    __syncthreads();   // everyone done reading the buffers before the next bulk copy lands
   }
 }
 
 // x = n + n*(r + ir) of ONE generate sub-step, before ROUND (reference :99-102), for every owned cell;
 // densities are not modified.  Diagnostic path for the "pre-rounding float update within 1e-6"
-// criterion: one thread per (cell, species), operands straight from global memory, runtime tile width.
-__global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, uint32_t R, double* __restrict__ out) {
+// criterion: one thread per (cell, species), operands straight from global memory, runtime tile width,
+// the same product formulation (fmaprod) as the hot kernel.
+__global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, uint32_t R, uint32_t fmaprod,
+                                                           double* __restrict__ out) {
   const Layout& L = p.L;
   const unsigned long long n = (unsigned long long)L.nx * L.ny * L.nsp;
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -146,16 +239,21 @@ __global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, ui
     const unsigned long long c = i / L.nsp;
     const uint32_t x = (uint32_t)(c % L.nx), yl = (uint32_t)(c / L.nx);
     const int32_t* tile = L.base + ((size_t)yl * L.ntx + x / L.tw) * L.tile_stride + x % L.tw;
-    const double d = i2d(tile[(size_t)s * L.tw]);
-    const double2 par = p.rowpar[s];
-    double ir = __dmul_rn(par.x, d);
+    const int nd = tile[(size_t)s * L.tw];
+    const double d = (double)(uint32_t)nd;
     const uint32_t b = s / R, rr = s % R;
-    for (uint32_t j = p.bptr[b]; j < p.bptr[b + 1]; ++j) {
-      const uint4 w = p.ell[(size_t)j * R + rr];
-      const double v = __hiloint2double((int)w.y, (int)w.x);
-      ir = __dadd_rn(ir, __dmul_rn(v, i2d(tile[w.z / 4])));   // w.z = col*TW*4 bytes
+    const uint32_t s0 = p.boff[b], W = p.boff[b + 1] - s0 - 1u;
+    const uint4* blk = p.stream + (size_t)s0 * R + rr;
+    const uint4 h = blk[0];
+    const double diag = dbl(h.x, h.y), r = dbl(h.z, h.w);
+    double ir = __dmul_rn(diag, d);
+    for (uint32_t j = 0; j < W; ++j) {
+      const uint4 w = blk[(size_t)(1 + j) * R];
+      const double v = dbl(w.x, w.y);
+      const int g = tile[w.z / 4];   // w.z = col*TW*4 bytes
+      ir = __dadd_rn(ir, fmaprod ? __fma_rn(v, bigu(g), dbl(w.x, w.w)) : __dmul_rn(v, (double)(uint32_t)g));
     }
-    out[i] = __dadd_rn(d, __dmul_rn(d, __dadd_rn(par.y, ir)));
+    out[i] = __dadd_rn(d, __dmul_rn(d, __dadd_rn(r, ir)));
   }
 }
 
