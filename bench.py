@@ -167,7 +167,7 @@ def build_model(E, args, nx, ny, comm, device, stream):
             getattr(m, k)(v)
     m.setGrid(nx, ny)
     m.seed(10)
-    for knob, val in (("gen_threads", args.gen_warps), ("gen_stages", args.gen_stages), ("gen_nofma", args.gen_nofma),
+    for knob, val in (("gen_threads", args.gen_warps), ("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem),
                       ("mig_variant", args.mig_variant)):
         if val:
             m.set_tuning(knob, val)
@@ -328,7 +328,7 @@ def main():
     ap.add_argument("--e2e-n", type=int, default=1024, dest="e2e_n")
     ap.add_argument("--gen-warps", type=int, default=0, dest="gen_warps")
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
-    ap.add_argument("--gen-nofma", type=int, default=0, dest="gen_nofma")
+    ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
     ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -112,11 +112,11 @@ class Engine {
   void last_kernel_config(int* grid, int* block, int* smem) const {
     *grid = last_grid_; *block = last_block_; *smem = last_smem_;
   }
-  // tuning knobs (bench/profiling): 0 = auto.  gen_variant: consumer warps of the generate pipeline (8/12/16/20/24);
-  // gen_stages: shared-memory tile buffers; gen_nofma: 1 forces the explicit-conversion product
+  // tuning knobs (bench/profiling): 0 = auto.  gen_variant: consumer warps of the generate pipeline (16/24/31);
+  // gen_stages: shared-memory tile buffers
   int gen_variant = 0;
   int gen_stages = 0;
-  int gen_nofma = 0;
+  int gen_nobsmem = 0;   // 1: never stage beta in shared memory
   int mig_variant = 0;
 
  private:
@@ -146,8 +146,7 @@ class Engine {
   // beta on device
   uint32_t nblocks_ = 0, beta_tw_ = 0, beta_nsp_ = 0;   // ELL blocks; the tile width / species count it was built for
   uint32_t* d_boff_ = nullptr; void* d_stream_ = nullptr;   // blocked-ELL stream (k_generate.cuh)
-  size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0;
-  bool beta_fma_ = false;                                   // every val admits the fused exact-product path
+  size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_slots_ = 0;
   BetaCsr beta_host_;                                   // kept to re-block when the tile width changes
 
   // scratch

@@ -5,19 +5,12 @@
 // ROWS = 128/TW at a time (one warp-op: ROWS rows x TW cells, a lane owns 4 consecutive cells of one row).
 // Block b occupies the 16-byte records  stream[boff[b]*ROWS ... boff[b+1]*ROWS):
 //     slot 0      : ROWS headers  { double diag ; double repro_rate }
-//     slot 1..W_b : ROWS terms    { val.lo, val.hi, byte offset of species row `col` inside a tile, hi word of c }
-// where W_b = longest row of the block (shorter rows are padded with val = 0, c = 0, offset 0) and
-// c = -val * 2^52, whose low word equals val's (exact power-of-two scaling), so only its high word is stored.
+//     slot 1..W_b : ROWS terms    { double val ; uint32 byte offset of species row `col` inside a tile ; pad }
+// where W_b = longest row of the block (shorter rows are padded with val = 0, offset 0).
 // A warp-op therefore reads its whole beta block through ONE base pointer with immediate offsets.
 // Terms of a row keep the COO order (reference oDiagIdx, :718-723) so the FP64 summation order is the reference's:
 //     ir = diag*n ; ir = ir + val_j*n[col_j] (j ascending) ; x = n + n*(r + ir), every operation individually rounded.
 //
-// The product val*n is formed as fma(val, 2^52 + n, -val*2^52): the fused operation rounds the EXACT value
-// val*(2^52+n) - val*2^52 = val*n once, i.e. it returns RN(val*n) -- bit-identical to the reference's separate
-// multiply -- while the int->double conversion of n costs nothing (2^52+n is the int paired with a constant high
-// word).  This removes one FP64-pipe instruction per term and cell; the accumulate stays a separate add.
-// The host only selects this path when every val is a normal double of moderate magnitude (FMAPROD), else the
-// kernel converts n explicitly and multiplies (same results, one more FP64 instruction per term).
 #pragma once
 #include "k_common.cuh"
 
@@ -31,19 +24,43 @@ struct GenParams {
   uint32_t seed, niter;
   unsigned long long t0;
   uint32_t nstages;          // pipeline kernel: shared-memory tile buffers
+  uint32_t stream_recs;      // records in `stream` (BSMEM kernels copy it into shared memory)
+  uint32_t rk[20];           // Philox round keys {k0_r, k1_r}, r = 0..9, for (seed, t0 >> 32): host-computed
 };
 
+template <bool BSMEM>
+__device__ __forceinline__ uint4 ldrec(const uint4* p) {
+  if (BSMEM) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+  }
+  return __ldg(p);
+}
+
+// Philox4x32-10 with the key schedule taken from kernel parameters (constant bank operands, no key arithmetic)
+__device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t (&rk)[20]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
+    const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk[2 * r];
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ rk[2 * r + 1];
+    c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
 __device__ __forceinline__ double dbl(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
-__device__ __forceinline__ double bigu(int n) { return __hiloint2double(0x43300000, n); }   // 2^52 + n, 0 <= n < 2^32
 
 // One warp-op: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of species row `row`.
-// `lp` = shared-memory tile + 4*quad (ints); `blk` = this lane's header record of block b; W = terms per row.
-template <int TW, bool FMAPROD>
-__device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, uint32_t row, const uint4* __restrict__ blk,
+// `lp` = shared-memory tile + 4*quad (ints); `own` = the lane's own densities; `blk` = this lane's header record of
+// block b (global memory, or the shared-memory copy when BSMEM); W = terms per row.
+template <int TW, bool BSMEM>
+__device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, const int4 own, const uint4* __restrict__ blk,
                                       uint32_t W, double x[4]) {
   constexpr int R = LaneMap<TW>::ROWS;
-  const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
-  const uint4 h = __ldg(blk);
+  const uint4 h = ldrec<BSMEM>(blk);
   const double diag = dbl(h.x, h.y), rr = dbl(h.z, h.w);
   const double d0 = (double)(uint32_t)own.x, d1 = (double)(uint32_t)own.y, d2 = (double)(uint32_t)own.z,
                d3 = (double)(uint32_t)own.w;
@@ -51,21 +68,15 @@ __device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, uint32_t r
   const uint4* e = blk + R;
 #pragma unroll 4
   for (uint32_t j = 0; j < W; ++j, e += R) {
-    const uint4 w = __ldg(e);
+    const uint4 w = ldrec<BSMEM>(e);
     const double v = dbl(w.x, w.y);
     const int4 g = *reinterpret_cast<const int4*>(reinterpret_cast<const char*>(lp) + w.z);
-    if (FMAPROD) {
-      const double c = dbl(w.x, w.w);
-      ir0 = __dadd_rn(ir0, __fma_rn(v, bigu(g.x), c));
-      ir1 = __dadd_rn(ir1, __fma_rn(v, bigu(g.y), c));
-      ir2 = __dadd_rn(ir2, __fma_rn(v, bigu(g.z), c));
-      ir3 = __dadd_rn(ir3, __fma_rn(v, bigu(g.w), c));
-    } else {
-      ir0 = __dadd_rn(ir0, __dmul_rn(v, (double)(uint32_t)g.x));
-      ir1 = __dadd_rn(ir1, __dmul_rn(v, (double)(uint32_t)g.y));
-      ir2 = __dadd_rn(ir2, __dmul_rn(v, (double)(uint32_t)g.z));
-      ir3 = __dadd_rn(ir3, __dmul_rn(v, (double)(uint32_t)g.w));
-    }
+    // int -> double on the conversion (XU) pipe, which is otherwise idle; multiply and accumulate stay two
+    // individually rounded FP64 operations (no contraction: -fmad=false)
+    ir0 = __dadd_rn(ir0, __dmul_rn(v, (double)(uint32_t)g.x));
+    ir1 = __dadd_rn(ir1, __dmul_rn(v, (double)(uint32_t)g.y));
+    ir2 = __dadd_rn(ir2, __dmul_rn(v, (double)(uint32_t)g.z));
+    ir3 = __dadd_rn(ir3, __dmul_rn(v, (double)(uint32_t)g.w));
   }
   x[0] = __dadd_rn(d0, __dmul_rn(d0, __dadd_rn(rr, ir0)));
   x[1] = __dadd_rn(d1, __dmul_rn(d1, __dadd_rn(rr, ir1)));
@@ -109,7 +120,7 @@ __device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t*
 //                    no CTA-wide barrier exists: a warp that is done with a tile moves on to the next one.
 // Results go straight from registers to HBM as 16-byte vectors (a warp-op writes 512 contiguous bytes), in place.
 // ---------------------------------------------------------------------------------------------------------
-template <int TW, int NW, bool FMAPROD>
+template <int TW, int NW, bool BSMEM>
 __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -119,9 +130,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)S * tile_bytes);
   uint64_t* empty = full + S;
   uint32_t* s_boff = reinterpret_cast<uint32_t*>(empty + S);
+  uint4* s_stream = reinterpret_cast<uint4*>(smem_raw + (((size_t)S * tile_bytes + 16 * S + 4 * (nblocks + 1)) + 15) / 16 * 16);
 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   for (uint32_t i = threadIdx.x; i <= nblocks; i += (NW + 1) * 32) s_boff[i] = p.boff[i];
+  if (BSMEM)
+    for (uint32_t i = threadIdx.x; i < p.stream_recs; i += (NW + 1) * 32) s_stream[i] = __ldg(p.stream + i);
+  const uint4* strm = BSMEM ? s_stream : p.stream;
   if (threadIdx.x == 0) {
     for (uint32_t s = 0; s < S; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, NW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -152,10 +167,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
     const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
     for (uint32_t b = first; b < nblocks; b += NW) {
       const uint32_t row = b * R + rr;
+      const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
+      // n = 0 stays 0 (x = 0 + 0*(...) = 0, ROUND(0) = 0): a warp-op whose 128 densities are all extinct is skipped
+      if (!__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) continue;
       const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
       double x[4];
-      gen_x<TW, FMAPROD>(lp, row, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
-      const int4 o = round4(x, draw4(xq, yg, row, p.t0, p.seed, 0u));
+      gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+      const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
       __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
     }
     first += NW - nbm;
@@ -170,7 +188,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
 // generate(niter > 1): per tile, `niter` Jacobi steps between two shared-memory buffers (HBM traffic amortised
 // over niter -- the scripts' cadence is generate(100), models/spatial_ecolab.py:67), CTA-wide barrier per step.
 // ---------------------------------------------------------------------------------------------------------
-template <int TW, int THREADS, bool FMAPROD>
+template <int TW, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -209,10 +227,14 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
       const int32_t* lp = src + 4 * q;
       for (uint32_t b = warp; b < nblocks; b += nwarps) {
         const uint32_t row = b * R + rr;
-        const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
-        double x[4];
-        gen_x<TW, FMAPROD>(lp, row, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
-        const int4 o = round4(x, draw4(xq, yg, row, p.t0 + step, p.seed, 0u));
+        const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
+        int4 o = make_int4(0, 0, 0, 0);
+        if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
+          const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
+          double x[4];
+          gen_x<TW, false>(lp, own, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+          o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
+        }
         *reinterpret_cast<int4*>(dst + row * TW + 4 * q) = o;
       }
       __syncthreads();
@@ -228,9 +250,8 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
 // x = n + n*(r + ir) of ONE generate sub-step, before ROUND (reference :99-102), for every owned cell;
 // densities are not modified.  Diagnostic path for the "pre-rounding float update within 1e-6"
 // criterion: one thread per (cell, species), operands straight from global memory, runtime tile width,
-// the same product formulation (fmaprod) as the hot kernel.
-__global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, uint32_t R, uint32_t fmaprod,
-                                                           double* __restrict__ out) {
+// the same operation order as the hot kernel.
+__global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, uint32_t R, double* __restrict__ out) {
   const Layout& L = p.L;
   const unsigned long long n = (unsigned long long)L.nx * L.ny * L.nsp;
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -251,7 +272,7 @@ __global__ void __launch_bounds__(256) pre_rounding_kernel(const GenParams p, ui
       const uint4 w = blk[(size_t)(1 + j) * R];
       const double v = dbl(w.x, w.y);
       const int g = tile[w.z / 4];   // w.z = col*TW*4 bytes
-      ir = __dadd_rn(ir, fmaprod ? __fma_rn(v, bigu(g), dbl(w.x, w.w)) : __dmul_rn(v, (double)(uint32_t)g));
+      ir = __dadd_rn(ir, __dmul_rn(v, (double)(uint32_t)g));
     }
     out[i] = __dadd_rn(d, __dmul_rn(d, __dadd_rn(r, ir)));
   }

@@ -934,7 +934,7 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   else if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
   else if (k == "mig_variant") m->eng.mig_variant = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
-  else if (k == "gen_nofma") m->eng.gen_nofma = value;
+  else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;
   else throw std::runtime_error("unknown tuning knob: " + k);
   ECO_CATCH
 }

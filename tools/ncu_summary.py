@@ -43,8 +43,10 @@ def main():
             print(f"    {h.split('issue_stalled_')[1].split('_per_issue')[0]:28s} {v:.3f}")
     # per-instruction view
     src = ncu(rep, "source", ("--print-source", "sass"))
-    if len(src) > 2:
-        h = src[0]
+    hi = next((i for i, r in enumerate(src) if "Source" in r and "Address" in r), None)
+    if hi is not None:
+        h = src[hi]
+        src = src[hi:]
         def col(name):
             for i, c in enumerate(h):
                 if c.strip() == name:
@@ -56,7 +58,11 @@ def main():
             ranked = sorted(((float(r[cs] or 0), i, r) for i, r in enumerate(src[1:]) if len(r) > cs and r[cs].replace('.', '').isdigit()), reverse=True)
             print(f"top SASS stall sites (of {tot:.0f} samples):")
             for v, i, r in ranked[:nsass]:
-                print(f"  {100 * v / max(tot, 1):5.1f}%  #{i:4d} exec={r[cx] if cx is not None else '?':>10s}  {r[ci][:90]}")
+                why = ""
+                sc = [(float(r[j] or 0), h[j]) for j in range(len(h)) if h[j].startswith("stall_") and "Not Issued" not in h[j] and j < len(r)]
+                if sc:
+                    why = max(sc)[1]
+                print(f"  {100 * v / max(tot, 1):5.1f}%  #{i:4d} exec={r[cx] if cx is not None else '?':>10s} {why:18s} {r[ci].strip()[:80]}")
 
 
 if __name__ == "__main__":

@@ -1,18 +1,20 @@
+# knob sweep at C3 (1024 x 1024 cells x 1024 species); output gpurun_out/sweep.log
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu2.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu2.log
 B="python bench.py --steps 10 --warmup 3 --nx 1024 --ny 1024 --no-cpu --no-e2e"
+P='import sys,json
+for l in sys.stdin:
+    if l.startswith("{"):
+        j=json.loads(l); print(j["roofline"]["kernels_ms_per_step"], "value %.3e"%j["value"])
+    else: print(l.rstrip()[:200])'
 : > gpurun_out/sweep.log
-for nw in 8 12 16 20 24; do for st in 2 3; do for nf in 0 1; do
-  echo "== nw=$nw stages=$st nofma=$nf" >> gpurun_out/sweep.log
-  timeout 120 $B --gen-warps $nw --gen-stages $st --gen-nofma $nf 2>&1 | python -c "
-import sys,json
-for l in sys.stdin:
-    if l.startswith('{'):
-        j=json.loads(l); print(j['roofline']['kernels_ms_per_step'], 'value %.3e'%j['value'])
-    else: print(l.rstrip()[:200])" >> gpurun_out/sweep.log
-done; done; done
-for nnz in 16 51; do for nf in 0 1; do echo "== nnz=$nnz nofma=$nf" >> gpurun_out/sweep.log; timeout 120 $B --nnz $nnz --gen-nofma $nf 2>&1 | python -c "
-import sys,json
-for l in sys.stdin:
-    if l.startswith('{'):
-        j=json.loads(l); print(j['roofline']['kernels_ms_per_step'], 'value %.3e'%j['value'])
-    else: print(l.rstrip()[:200])" >> gpurun_out/sweep.log; done; done
+run() { echo "== $*" >> gpurun_out/sweep.log; timeout 120 $B "$@" 2>&1 | python -c "$P" >> gpurun_out/sweep.log; }
+run
+run --gen-warps 31
+run --gen-warps 16
+run --mig-variant 1
+run --mig-variant 2
+run --mig-variant 3
+run --nnz 16
+run --nnz 16 --gen-warps 31
+run --nnz 51
+run --nnz 51 --gen-warps 31
