@@ -236,14 +236,18 @@ def run_native(args):
     k_ms, k_n = kt[name]
     bytes_per_launch = 8.0 * local_updates            # 4 B read + 4 B written per cell-species update
     achieved = bytes_per_launch / (k_ms / max(k_n, 1) * 1e-3) / 1e9 if k_ms > 0 else 0.0
-    traffic = None
+    # DRAM traffic of that kernel from the committed ncu --set full capture (profiles/traffic.json: bytes per update
+    # measured at C3, 1024 x 1024 x 1024, same kernel and nnz/row), scaled to this launch's updates
+    traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        tj = json.load(open(tp))
-        key = f"{name}:{nx}x{ny}x{args.nsp}:nnz{args.nnz}"
-        traffic = tj.get(key, {}).get("dram_bytes_per_launch")
-    roofline = {"bound": "hbm", "kernel": name + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+        ent = json.load(open(tp)).get(f"{name}:nnz{args.nnz}")
+        if ent and args.nsp == ent.get("nsp"):
+            traffic = ent["dram_bytes_per_update"] * local_updates
+            traffic_src = ent["source"]
+    kname = {"generate": "generate_pipe_kernel", "migrate": "migrate_kernel"}.get(name, name)
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": k_ms / max(k_n, 1),
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]},
                 "step_frac_at_16B": (16.0 * updates_per_step / world * args.steps / (ms * 1e-3) / 1e9) / peak}

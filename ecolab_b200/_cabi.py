@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libecolab_b200.so")
+LIB_PATH = os.environ.get("ECOLAB_B200_LIB") or os.path.join(_HERE, "libecolab_b200.so")   # override: profiling builds only
 
 
 class EcolabError(RuntimeError):

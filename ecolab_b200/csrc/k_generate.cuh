@@ -172,9 +172,18 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       if (!__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) continue;
       const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
       double x[4];
+#ifndef ECO_ABLATE
       gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
       const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
       __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
+#else   // cost-attribution builds (tools/ablate.sh): results are wrong on purpose, never shipped
+      gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, (ECO_ABLATE & 2) ? 0u : s1 - s0 - 1u, x);
+      const uint4 u = (ECO_ABLATE & 1) ? make_uint4(row, row * 3u, xq, yg) : philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk);
+      int4 o;
+      if (ECO_ABLATE & 4) o = make_int4(__double2loint(x[0]) ^ u.x, __double2loint(x[1]) ^ u.y, __double2loint(x[2]) ^ u.z, __double2loint(x[3]) ^ u.w);
+      else o = round4(x, u);
+      if (!(ECO_ABLATE & 8) || o.x == 0x7fffffff) __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
+#endif
     }
     first += NW - nbm;
     if (first >= NW) first -= NW;

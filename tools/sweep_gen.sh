@@ -9,12 +9,4 @@ for l in sys.stdin:
 : > gpurun_out/sweep.log
 run() { echo "== $*" >> gpurun_out/sweep.log; timeout 120 $B "$@" 2>&1 | python -c "$P" >> gpurun_out/sweep.log; }
 run
-run --gen-warps 31
-run --gen-warps 16
 run --mig-variant 1
-run --mig-variant 2
-run --mig-variant 3
-run --nnz 16
-run --nnz 16 --gen-warps 31
-run --nnz 51
-run --nnz 51 --gen-warps 31
