@@ -289,6 +289,8 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     import ctypes as C
 
     def one():
+        if world == 1 and not args.e2e_unpipelined:
+            return m.step_host(a_in, a_out, 1)     # eco_step_host: banded H2D / kernels / D2H pipeline
         E._cabi.check(m._L.eco_set_density_all(m._h, C.c_void_p(a_in.ctypes.data), nloc, args.nsp))
         moved = m.step(1)
         E._cabi.check(m._L.eco_get_density_all(m._h, C.c_void_p(a_out.ctypes.data), nloc, args.nsp))
@@ -316,7 +318,9 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     del m
     return {"value": val, "unit": UNIT, "h2d_bytes_per_step": int(nx * ny * args.nsp * 4), "d2h_bytes_per_step": int(nx * ny * args.nsp * 4 + 8),
             "workload": f"spatial {nx}x{ny} cells x {args.nsp} species through host buffers (bounded: pinned host copy of the full "
-                        f"grid per step)", "steps": steps, "ms_per_step": ms / steps}
+                        f"grid per step)", "steps": steps, "ms_per_step": ms / steps,
+            "call": "eco_step_host (row-banded H2D/kernel/D2H pipeline)" if world == 1 and not args.e2e_unpipelined
+                    else "eco_set_density_all + eco_step + eco_get_density_all"}
 
 
 def main():
@@ -334,6 +338,7 @@ def main():
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
     ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
     ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")
+    ap.add_argument("--e2e-unpipelined", action="store_true", dest="e2e_unpipelined")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

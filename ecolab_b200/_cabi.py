@@ -55,6 +55,7 @@ SIGNATURES = {
     "eco_generate": [_vp, C.c_uint],
     "eco_migrate": [_vp, _P(_u64)],
     "eco_step": [_vp, C.c_uint, _P(_u64)],
+    "eco_step_host": [_vp, _vp, _vp, _sz, _sz, C.c_uint, _P(_u64)],
     "eco_condense": [_vp, _P(C.c_uint)],
     "eco_mutate": [_vp],
     "eco_random_interaction": [_vp, C.c_uint, _dbl],

@@ -76,6 +76,10 @@ Engine::~Engine() {
   free_buffers();
   cudaFree(d_boff_); cudaFree(d_stream_);
   cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_stage_);
+  for (auto& p : d_band_) cudaFree(p);
+  for (auto& e : ev_band_) if (e) cudaEventDestroy((cudaEvent_t)e);
+  if (st_in_) cudaStreamDestroy((cudaStream_t)st_in_);
+  if (st_out_) cudaStreamDestroy((cudaStream_t)st_out_);
   cudaFreeHost(h_total_);
   if (ev_total_) cudaEventDestroy((cudaEvent_t)ev_total_);
   for (auto& e : ev_pending_) { cudaEventDestroy((cudaEvent_t)e.start); cudaEventDestroy((cudaEvent_t)e.stop); }

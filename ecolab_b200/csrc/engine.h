@@ -67,9 +67,13 @@ class Engine {
   // ---- hot path -------------------------------------------------------------
   // niter fused Lotka-Volterra steps on every owned cell; t0 = absolute tstep of the first
   void generate(uint32_t niter, uint64_t t0, uint32_t seed);
+  void generate_rows(uint32_t niter, uint64_t t0, uint32_t seed, uint32_t r0, uint32_t nrows);
   // cm[s] = capped migration coefficient; returns sum |delta| over owned cells (not halved)
   uint64_t migrate(const double* cm_host, bool wait_result = true);
   uint64_t migrate_result();   // blocks on the async total of the last migrate
+  // generate(niter) + migrate with HOST cell-major buffers [cell][nsp] in and out, streamed in bands of grid rows:
+  // H2D of band k+1, the kernels of band k and D2H of band k-1 overlap (full-duplex PCIe); returns sum |delta|
+  uint64_t step_host(const int32_t* in_host, int32_t* out_host, uint32_t niter, uint64_t t0, uint32_t seed, const double* cm_host);
   // alive[s] = 1 iff some owned cell has density != 0
   void alive_mask(uint8_t* alive_host);
   // compact species rows: keep[s] != 0 survives, order preserved
@@ -121,6 +125,8 @@ class Engine {
 
  private:
   void ensure_other();
+  void migrate_prepare(const double* cm_host);
+  void migrate_rows(uint32_t r0, uint32_t nrows);
   void alloc_buffers(uint32_t cap);
   void build_ell();
   void ensure_vec(size_t n);
@@ -156,6 +162,9 @@ class Engine {
   unsigned long long* h_total_ = nullptr;              // pinned
   MutRecord* d_rec_ = nullptr; size_t rec_cap_ = 0;
   int32_t* d_stage_ = nullptr; size_t stage_cap_ = 0;  // cell-major staging
+  int32_t* d_band_[4] = {nullptr, nullptr, nullptr, nullptr}; size_t band_cap_ = 0;   // step_host: 2 in + 2 out band stagings
+  void* st_in_ = nullptr; void* st_out_ = nullptr;       // copy streams of step_host
+  void* ev_band_[8] = {nullptr};
   void* ev_total_ = nullptr;
 
   uint64_t launches_ = 0;

@@ -32,17 +32,6 @@ __device__ __forceinline__ int flux(double c, double ba, double bb) {
   return __double2int_rz(__dmul_rn(c, __dadd_rn(ba, -bb)));
 }
 
-// the same without the conversion (XU) pipe: trunc toward zero through a directed-rounding add on |y| against 2^52
-// (exact for |y| < 2^31, guaranteed by c <= 1/maxNbrs), sign restored with integer ops
-__device__ __forceinline__ int flux_magic(double c, double ba, double bb) {
-  const double y = __dmul_rn(c, __dadd_rn(ba, -bb));
-  const int k = __double2loint(__dadd_rz(fabs(y), TWO52));
-  const int s = __double2hiint(y) >> 31;
-  return (k ^ s) - s;
-}
-template <bool MAGIC>
-__device__ __forceinline__ int fluxv(double c, double ba, double bb) { return MAGIC ? flux_magic(c, ba, bb) : flux(c, ba, bb); }
-
 struct MigRow {
   int4 v;      // this lane's 4 cells
   int l, r;    // neighbour cells across the tile boundary (only meaningful on the first / last quad)
@@ -61,7 +50,7 @@ __device__ __forceinline__ MigRow mig_load(const int32_t* rowbase, size_t lane_o
 }
 
 // horizontal net flux of the 4 cells: hs_k = T(west_k - own_k) - T(own_k - east_k)
-template <int TW, bool MAGIC>
+template <int TW>
 __device__ __forceinline__ int4 mig_horizontal(const MigRow& m, double c, uint32_t q, bool has_l, bool has_r,
                                                bool ragged, uint32_t x0, uint32_t nx) {
   constexpr int QPR = LaneMap<TW>::QPR;
@@ -70,9 +59,9 @@ __device__ __forceinline__ int4 mig_horizontal(const MigRow& m, double c, uint32
   if (q == 0) lw = m.l;
   if (!has_l) lw = v.x;                                  // no west neighbour: zero difference
   const double b0 = big(v.x), b1 = big(v.y), b2 = big(v.z), b3 = big(v.w);
-  int t0 = fluxv<MAGIC>(c, big(lw), b0), t1 = fluxv<MAGIC>(c, b0, b1), t2 = fluxv<MAGIC>(c, b1, b2), t3 = fluxv<MAGIC>(c, b2, b3);
+  int t0 = flux(c, big(lw), b0), t1 = flux(c, b0, b1), t2 = flux(c, b1, b2), t3 = flux(c, b2, b3);
   const int re = has_r ? m.r : v.w;
-  int te = fluxv<MAGIC>(c, b3, big(re));                         // west flux of the east tile's first cell
+  int te = flux(c, b3, big(re));                         // west flux of the east tile's first cell
   if (ragged) {                                          // last tile of a row wider than the grid: padding cells hold 0
     if (x0 >= nx) t0 = 0;
     if (x0 + 1 >= nx) t1 = 0;
@@ -90,9 +79,7 @@ __device__ __forceinline__ int4 mig_vertical(const int4& up, const int4& own, do
                    flux(c, big(up.w), big(own.w)));
 }
 
-// PF > 0: one lane per warp asks the TMA unit to pull the warp's 512 contiguous bytes of grid row y+PF into L2
-// (cp.async.bulk.prefetch.L2), so the register-staged loads two rows ahead find their data on chip.
-template <int TW, int PF, bool MAGIC>
+template <int TW>
 __global__ void __launch_bounds__(256) migrate_kernel(const MigParams p) {
   constexpr int R = LaneMap<TW>::ROWS, QPR = LaneMap<TW>::QPR;
   const Layout& L = p.L;
@@ -125,16 +112,12 @@ __global__ void __launch_bounds__(256) migrate_kernel(const MigParams p) {
       const int4 up = *reinterpret_cast<const int4*>(rowbase((int)ys - 1) + lane_off);
       tn = mig_vertical(up, cur.v, c);
     }
-    int4 hs = mig_horizontal<TW, MAGIC>(cur, c, q, has_l, has_r, ragged, x0, L.nx);
+    int4 hs = mig_horizontal<TW>(cur, c, q, has_l, has_r, ragged, x0, L.nx);
     bool has_nxt = L.y0 + ys + 1 < L.nyg;
     MigRow nxt = cur;
     if (has_nxt) nxt = mig_load<TW>(rowbase((int)ys + 1), lane_off, L.tile_stride, edge_l, edge_r);
     int32_t* dp = p.dst + (size_t)ys * L.row_stride + lane_off;
-    const size_t warp_off = lane_off - ((size_t)rr * TW + 4 * q);   // first int of the warp's 512-byte block in a grid row
-    if (PF > 0 && lane == 0)
-      for (uint32_t k = 2; k < (uint32_t)PF && ys + k < ye; ++k) bulk_prefetch_l2(rowbase((int)(ys + k)) + warp_off, 512u);
     for (uint32_t y = ys; y < ye; ++y) {
-      if (PF > 0 && lane == 0 && y + PF < ye) bulk_prefetch_l2(rowbase((int)(y + PF)) + warp_off, 512u);
       // issue the loads of row y+2 before the arithmetic on row y+1 (register double buffering)
       const bool has_nn = y + 2 <= ye && L.y0 + y + 2 < L.nyg && y + 1 < ye;
       MigRow nn = nxt;
@@ -142,7 +125,7 @@ __global__ void __launch_bounds__(256) migrate_kernel(const MigParams p) {
       int4 ts = make_int4(0, 0, 0, 0), hn = hs;
       if (has_nxt) {
         ts = mig_vertical(cur.v, nxt.v, c);          // north flux of row y+1 = minus the south flux of row y
-        if (y + 1 < ye) hn = mig_horizontal<TW, MAGIC>(nxt, c, q, has_l, has_r, ragged, x0, L.nx);
+        if (y + 1 < ye) hn = mig_horizontal<TW>(nxt, c, q, has_l, has_r, ragged, x0, L.nx);
       }
       const int d0 = tn.x - ts.x + hs.x, d1 = tn.y - ts.y + hs.y, d2 = tn.z - ts.z + hs.z, d3 = tn.w - ts.w + hs.w;
       *reinterpret_cast<int4*>(dp) = make_int4(cur.v.x + d0, cur.v.y + d1, cur.v.z + d2, cur.v.w + d3);

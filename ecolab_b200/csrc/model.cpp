@@ -195,6 +195,30 @@ struct eco_model {
     return total;
   }
 
+  // generate(niter) then migrate() fed from / drained to host buffers (cell-major [cell][nsp], ascending cell id)
+  uint64_t step_host(const int32_t* in, int32_t* out, size_t ncells, size_t ns, unsigned niter) {
+    if (panmictic || y0 != 0 || nyl != numY) throw std::runtime_error("step_host: needs an unpartitioned spatial grid");
+    if (ncells != ncells_local()) throw std::runtime_error("step_host: cell count differs from the grid");
+    if (tstep == 0) makeConsistent();
+    grow_engine(std::max(ns, nsp()));
+    check_sizes(true);
+    if (ns != nsp()) throw std::runtime_error("step_host: species count differs from the model");
+    upload();
+    const size_t n = nsp();
+    std::vector<double> cm(n);
+    const double cap = 1.0 / maxNbrs;                                   // :628
+    const uint64_t t_after = tstep + niter;
+    for (size_t s = 0; s < n; ++s) {
+      const double mm = (t_after - last_mig_tstep) * migration[s];      // :626 (migrate runs after tstep += niter)
+      cm[s] = mm > cap ? cap : mm;                                      // :629
+    }
+    const uint64_t total = n ? eng.step_host(in, out, niter, tstep, seed, cm.data()) : 0;
+    tstep = t_after;
+    salt_t = tstep;
+    last_mig_tstep = tstep;
+    return total;
+  }
+
   // ModelData::condense :139-159
   void condenseModel(const std::vector<uint8_t>& mask) {
     const size_t n = nsp();
@@ -679,6 +703,14 @@ int eco_step(eco_model* m, unsigned niter, uint64_t* total) {
   m->generate(niter);
   const uint64_t t = m->migrate_local();
   if (total) *total = t / 2;
+  ECO_CATCH
+}
+int eco_step_host(eco_model* m, const int32_t* in, int32_t* out, size_t ncells, size_t nsp, unsigned niter, uint64_t* total) {
+  ECO_TRY
+  need(m);
+  if (!in || !out) throw std::runtime_error("step_host: null buffer");
+  const uint64_t t = m->step_host(in, out, ncells, nsp, niter);
+  if (total) *total = t / 2;   // :702
   ECO_CATCH
 }
 int eco_migrate_local(eco_model* m, uint64_t* total) {

@@ -315,6 +315,18 @@ class SpatialModel(EcolabModelBase):
         self.generate(niter)
         return self.migrate()
 
+    def step_host(self, dens_in, dens_out, niter=1):
+        """generate(niter) + migrate() on a HOST-resident state: `dens_in` [cell][nsp] int32 is uploaded, the result
+        lands in `dens_out`; copies and kernels are pipelined over bands of grid rows (eco_step_host)."""
+        if self.world != 1:
+            raise EcolabError("step_host: unpartitioned grids only")
+        a, b = np.ascontiguousarray(dens_in, dtype=np.int32), dens_out
+        if b.dtype != np.int32 or not b.flags.c_contiguous or b.shape != a.shape:
+            raise EcolabError("step_host: dens_out must be a C-contiguous int32 array shaped like dens_in")
+        t = C.c_uint64()
+        check(self._L.eco_step_host(self._h, _ptr(a), _ptr(b), a.shape[0], a.shape[1], int(niter), C.byref(t)))
+        return t.value
+
     def condense(self):
         if self.world == 1:
             return super().condense()

@@ -108,6 +108,12 @@ int eco_migrate(eco_model* m, uint64_t* total);
 /* one driver-loop body of the spatial scripts (models/spatial_ecolab.py:67-69 minus mutate):
  * eco_generate(niter) followed by eco_migrate(total) as one call (fewer host round trips) */
 int eco_step(eco_model* m, unsigned niter, uint64_t* total);
+/* the same body for a HOST-resident state: densities come from `in` and the result goes to `out` (both cell-major
+ * [cell][nsp], ascending cell id, as eco_set/get_density_all; pinned memory makes the copies asynchronous).  Equivalent
+ * to eco_set_density_all(in); eco_step(niter); eco_get_density_all(out) -- i.e. SpatialModel::generate :607-614 +
+ * ::migrate :616-703 on densities set through EcolabPoint::density (models/ecolab_model.h:88) -- but streamed in
+ * bands of grid rows so that H2D, the kernels and D2H overlap.  Unpartitioned grids only. */
+int eco_step_host(eco_model* m, const int32_t* in, int32_t* out, size_t ncells, size_t nsp, unsigned niter, uint64_t* total);
 /* SpatialModel::condense :171-196 / PanmicticModel::condense :161-169; *removed = #extinct species */
 int eco_condense(eco_model* m, unsigned* removed);
 /* SpatialModel::mutate :215-276 / PanmicticModel::mutate :205-213 */

@@ -102,6 +102,23 @@ def test_step_equals_generate_then_migrate(oracle_mod, gpu):
         assert np.array_equal(m.density_array(), o.get_density_all())
 
 
+@pytest.mark.parametrize("grid,nsp,k,niter", [((70, 9), 129, 3, 1), ((33, 40), 64, 16, 1), ((8, 5), 37, 3, 4), ((5, 1), 9, 2, 1)])
+def test_step_host_banded_pipeline(oracle_mod, gpu, grid, nsp, k, niter):
+    """eco_step_host = set_density_all + generate(niter) + migrate + get_density_all, streamed in row bands."""
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k, mig=0.07)
+    d_in = oracle_density(o, grid).copy()
+    out = np.empty_like(d_in)
+    for it in range(3):
+        o.set_density_all(d_in)
+        o.generate(niter); want_moved = o.migrate()
+        moved = m.step_host(d_in, out, niter)
+        assert moved == want_moved
+        assert np.array_equal(out, o.get_density_all()), f"step {it}"
+        assert np.array_equal(m.density_array(), out)            # the device state is the same result
+        assert m.tstep() == int(o.get("tstep")) and m.last_mig_tstep() == m.tstep()
+        d_in = out.copy()
+
+
 @pytest.mark.parametrize("grid,nsp,k", [(None, 100, 3), ((8, 5), 37, 3), ((70, 9), 129, 3)])
 def test_condense_bit_exact(oracle_mod, gpu, grid, nsp, k):
     ncells = grid[0] * grid[1] if grid else 1
