@@ -122,16 +122,22 @@ def cpu_leg(nsp, nnz, steps, warmup, budget_s=20.0):
                       f"(oracle restatement of the reference OpenMP path, g++ -O3 -fopenmp -ffp-contract=off)"}, dt / steps * 1e3
 
 
+def workload_name(nx, ny, nsp):
+    return f"spatial {nx}x{ny} cells x {nsp} species, generate(1)+migrate() per step"
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cb, ms = cpu_leg(args.nsp, args.nnz, args.steps, args.warmup, budget_s=60.0)
+    nx, ny = (args.nx, args.ny) if args.nx and args.ny else (4096, 4096)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64->i32", "data": "synthetic",
-            "config": {"workload": cb["sample"], "note": "reference CPU algorithm on host cores; the reference build itself "
-                       "needs the absent classdesc submodule, so this is the line-by-line oracle restatement"},
+            "config": {"workload": workload_name(nx, ny, args.nsp), "nnz_per_row": args.nnz, "sample": cb["sample"],
+                       "note": "reference CPU algorithm on host cores, each step a bounded strip of the workload; the reference "
+                               "build itself needs the absent classdesc submodule, so this is the line-by-line oracle restatement"},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -266,7 +272,7 @@ def run_native(args):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64->i32", "data": "synthetic",
-                "config": {"workload": f"spatial {nx}x{ny} cells x {args.nsp} species, generate(1)+migrate() per step",
+                "config": {"workload": workload_name(nx, ny, args.nsp),
                            "nnz_per_row": args.nnz, "partition": f"{world} row slab(s)", "l2": "inputs (%.1f GiB) larger than L2" % (updates_per_step * 4 / 2**30),
                            "rng": "Philox4x32-10 keyed (seed, cell, slot, tstep)", "migrated_last_step": int(moved)},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
