@@ -17,6 +17,7 @@
 #include "k_generate.cuh"
 #include "k_migrate.cuh"
 #include "k_misc.cuh"
+#include "k_dense.cuh"
 
 #define CK(x) ::eco::check_cuda((int)(x), #x, __FILE__, __LINE__)
 #define ST ((cudaStream_t)stream_)
@@ -75,6 +76,8 @@ Engine::~Engine() {
   cudaDeviceSynchronize();
   free_buffers();
   cudaFree(d_boff_); cudaFree(d_stream_);
+  cudaFree(d_aop_); cudaFree(d_bop_); cudaFree(d_dsp_); cudaFree(d_partial_); cudaFree(d_maxn_);
+  if (h_maxn_) cudaFreeHost(h_maxn_);
   cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_stage_);
   for (auto& p : d_band_) cudaFree(p);
   for (auto& e : ev_band_) if (e) cudaEventDestroy((cudaEvent_t)e);
@@ -290,5 +293,6 @@ void Engine::fill_density_random(uint32_t seed, int32_t lo, int32_t hi) {
 }
 
 #include "engine_ops.inc"
+#include "engine_dense.inc"
 
 }  // namespace eco

@@ -103,7 +103,7 @@ class Engine {
   void pre_rounding(double* out_host);
 
   // per-kernel device timing (CUDA events on the engine stream), off by default
-  enum KernelKind { K_GENERATE = 0, K_MIGRATE = 1, K_STEP = 2, K_COUNT = 3 };
+  enum KernelKind { K_GENERATE = 0, K_MIGRATE = 1, K_STEP = 2, K_DENSE_PACK = 3, K_DENSE_MMA = 4, K_COUNT = 5 };
   bool timing = false;
   void kernel_times(double* ms, uint64_t* count);   // arrays of K_COUNT; synchronises the stream
   void reset_kernel_times();
@@ -122,6 +122,13 @@ class Engine {
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory
   int mig_variant = 0;
+  // dense (tensor-core) generate, k_dense.cuh.  gen_dense: 0 = automatic (beta at least half full and >= 128 species),
+  // 1 = always, -1 = never.  dense_slices = P, the 8-bit slices beta is cut into (3: 2^-24 of the row maximum; 7: FP64).
+  int gen_dense = 0;
+  int dense_slices = 3;
+  bool dense_wanted() const;
+  uint32_t dense_last_q() const { return dense_q_; }        // density slices used by the last dense generate
+  uint64_t dense_mma_per_step() const { return dense_macs_; }   // integer MACs issued by the last dense generate step
 
  private:
   void ensure_other();
@@ -129,6 +136,8 @@ class Engine {
   void migrate_rows(uint32_t r0, uint32_t nrows);
   void alloc_buffers(uint32_t cap);
   void build_ell();
+  void build_dense();
+  void generate_dense(uint32_t niter, uint64_t t0, uint32_t seed, uint32_t r0, uint32_t nrows, double* xout_dev);
   void ensure_vec(size_t n);
   void ensure_mask(size_t n);
   void free_buffers();
@@ -155,6 +164,16 @@ class Engine {
   size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_slots_ = 0;
   BetaCsr beta_host_;                                   // kept to re-block when the tile width changes
 
+  // dense path operands (k_dense.cuh)
+  uint8_t* d_aop_ = nullptr; size_t aop_cap_ = 0;       // beta slices, shared-memory image layout
+  uint8_t* d_bop_ = nullptr; size_t bop_cap_ = 0;       // density slices of one row band
+  double* d_dsp_ = nullptr; size_t dsp_cap_ = 0;        // diag | repro_rate | 2^-s per padded species row
+  double* d_partial_ = nullptr; size_t partial_cap_ = 0;
+  unsigned int* d_maxn_ = nullptr; unsigned int* h_maxn_ = nullptr;
+  uint32_t dense_p_ = 0, dense_nsp_ = 0, dense_mtiles_ = 0, dense_nkc_ = 0, dense_q_ = 1;
+  uint64_t dense_macs_ = 0;
+  uint64_t beta_version_ = 0, dense_version_ = ~0ull;
+
   // scratch
   double* d_vec_ = nullptr; size_t vec_cap_ = 0;       // per-species doubles (cm / ms)
   uint8_t* d_mask_ = nullptr; uint32_t* d_map_ = nullptr; size_t mask_cap_ = 0;
@@ -173,8 +192,8 @@ class Engine {
   struct PendingEvent { void* start; void* stop; int kind; };
   std::vector<PendingEvent> ev_pending_;
   std::vector<void*> ev_pool_;
-  double kt_ms_[K_COUNT] = {0, 0, 0};
-  uint64_t kt_n_[K_COUNT] = {0, 0, 0};
+  double kt_ms_[K_COUNT] = {};
+  uint64_t kt_n_[K_COUNT] = {};
   void time_begin(int kind);
   void time_end();
 };

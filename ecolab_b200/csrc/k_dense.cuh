@@ -1,0 +1,345 @@
+// k_dense.cuh -- generate() for a genuinely dense interaction matrix: the contraction  S[i,c] = sum_j beta[i,j] n[j,c]
+// on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM), with the rest of
+// EcolabPoint::generate (reference models/ecolab_model.cc:90-112) and ROUND (:57-66) fused into the epilogue.
+//
+// Exact-integer slicing (Ozaki-style): per species row i,  beta[i,j] * 2^s_i  is rounded to an integer F[i,j] of
+// 8P-1 bits and written in balanced radix 256,  F = sum_p a_p 256^(P-1-p),  a_p in [-128,127]  (A operand, s8);
+// a density is  n = sum_q b_q 256^q,  b_q in [0,255]  (B operand, u8).  Every slice product a_p x b_q is an
+// s8 x u8 -> s32 GEMM whose K-sum is EXACT (8192 x 128 x 255 < 2^31 leaves room for 8 products per accumulator);
+// products of equal weight 256^g, g = q-p+P-1, share one TMEM accumulator ("group").  The epilogue recombines
+//     S = 2^-s_i * sum_g 256^g acc_g            (Horner in FP64: exact while the integer stays below 2^53)
+//     ir = diag*n + S ;  x = n + n*(r + ir) ;  n' = ROUND(x)   with the same Philox draw as the sparse kernel.
+// The only approximation is the rounding of beta to 8P-1 bits relative to its row maximum (P = 3: 2^-24, P = 7:
+// beyond FP64), so the pre-rounding x agrees with the FP64 sequential sum to ~1e-9 (P = 3) and the integer results
+// differ from the oracle only where that error flips a ROUND threshold; with beta entries that are dyadic rationals
+// the path is bit-exact (tests/test_gpu_dense.py).  It cannot reproduce the reference's FP64 summation ORDER, which
+// is why the sparse kernel stays the default and this path is selected only for dense beta (Engine::dense_wanted).
+//
+// Operands live in HBM as ready-made shared-memory images, so a pipeline stage is filled by two 1-D bulk copies
+// (TMA unit, SASS UBLKCP) and needs no tensor map: un-swizzled K-major "core matrix" layout
+//     tile[k16 = KC/16][row group = 16][row = 8][16 bytes]       (128 rows x KC bytes of K)
+// for which the tcgen05 shared-memory descriptor is  LBO = 2048 (stride between 16-byte K chunks), SBO = 128
+// (stride between 8-row groups) -- pinned on B200 by tools/umma_probe.cu (profiles/r1_umma_probe.txt).
+//     A: [m_tile][kc][p]  -> P consecutive tiles = one bulk copy        (built once per beta upload, host side)
+//     B: [n_tile][kc][q]  -> Q consecutive tiles = one bulk copy        (dense_pack_kernel, every timestep)
+// N runs over the padded cell quads of the slab in (row, x) order: N index = 4*(yl*nxq + xq) + e.
+//
+// Kernel = persistent, one CTA per SM, warp-specialised:
+//   warp 0 : producer   -- bulk copies of stage (tile, kc) into a ring, "full"/"empty" mbarriers
+//   warp 1 : MMA issuer -- one lane issues P*Q*(KC/32) tcgen05.mma per stage into <= 4 accumulators of 128 columns,
+//                          tcgen05.commit frees the stage / publishes the accumulators
+//   warps 2..9 : epilogue -- tcgen05.ld (lane = species row, 64 columns per warp), Horner, generate arithmetic,
+//                            Philox ROUND, STG.128; the densities of the next 16 columns are prefetched meanwhile
+#pragma once
+#include "k_common.cuh"
+#include "k_generate.cuh"
+
+namespace eco {
+
+constexpr uint32_t DENSE_KC = 64;                    // K bytes (species) per pipeline stage and operand tile
+constexpr uint32_t DENSE_TILE_BYTES = 128 * DENSE_KC;   // one 128-row operand tile
+constexpr uint32_t DENSE_MAX_GROUPS = 4;             // 4 accumulators x 128 columns = the 512 TMEM columns
+constexpr uint32_t DENSE_EPI_WARPS = 8;               // two per TMEM lane quadrant, 64 accumulator columns each
+constexpr uint32_t DENSE_THREADS = (2 + DENSE_EPI_WARPS) * 32;
+
+struct DenseParams {
+  Layout L;                    // densities of the rows this launch covers
+  const uint8_t* aop;          // beta slices (see above)
+  const uint8_t* bop;          // density slices
+  const double* diag;          // [mtiles*128] interaction.diag (0 in the padding)
+  const double* rr;            // [mtiles*128] repro_rate
+  const double* rscale;        // [mtiles*128] 2^-s_i
+  double* partial;             // [ntn][mtiles][128 cols][128 rows] running sums between group rounds, or null
+  double* xout;                // cell-major [cell][nsp] pre-rounding x (diagnostic), or null
+  uint32_t P, Q;               // slices of beta / of the densities
+  uint32_t g0, g1;             // groups [g0, g1) handled by this launch (g1 - g0 <= 4)
+  double w0;                   // 256^g0, the weight of the lowest group of this launch
+  uint32_t flags;              // 1: add `partial` to this round's sum   2: store the sum to `partial`, no epilogue
+  uint32_t nkc, mtiles, ntn;   // K chunks, 128-row species tiles, 128-column cell tiles
+  uint32_t mblock;             // species tiles per L2 super-block (tile order: [m block][n tile][m in block])
+  uint32_t nxq;                // padded quads per grid row = ntx*TW/4
+  uint32_t nstages;
+  unsigned long long t0;
+  uint32_t rk[20];             // Philox key schedule (as GenParams)
+};
+
+// ---- tcgen05 wrappers ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {   // LBO 2048 B, SBO 128 B, version 1, no swizzle
+  return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)(2048u >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+               "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+               : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {   // arrives on `bar` when all MMAs issued so far have completed
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// 16 consecutive 32-bit columns of this thread's TMEM lane (returns when the data is in the registers)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, int (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"   // same statement: no use of v[] can be scheduled before the wait
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// mbarrier wait with a watchdog: a mis-programmed pipeline traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+    if (done) return;
+    if ((spin & 1023u) == 1023u && clock64() - t0 > 8000000000ll) __trap();   // ~4 s
+  }
+}
+
+// tile id -> (species tile, cell tile); false for the padding of the last super-block
+__device__ __forceinline__ bool dense_tile(const DenseParams& p, uint32_t id, uint32_t& mt, uint32_t& nt) {
+  const uint32_t per = p.mblock * p.ntn;
+  const uint32_t blk = id / per, rem = id - blk * per;
+  nt = rem / p.mblock;
+  mt = blk * p.mblock + (rem - nt * p.mblock);
+  return mt < p.mtiles;
+}
+
+// ---- B operand: int32 densities -> Q u8 slices in the shared-memory image layout ---------------------------------------
+// One thread = 16 consecutive species x one cell quad: 16 LDG.128 (contiguous 256 B when TW = 4) -> 4*Q STG.128.
+__global__ void __launch_bounds__(256) dense_pack_kernel(const Layout L, uint8_t* __restrict__ bop, uint32_t Q, uint32_t nkc,
+                                                         uint32_t ntn, uint32_t nxq, unsigned int* __restrict__ maxn) {
+  const uint32_t k16_total = nkc * (DENSE_KC / 16);
+  const unsigned long long nquads = (unsigned long long)ntn * 32;   // padded: 32 quads per cell tile
+  const unsigned long long nwork = nquads * k16_total;
+  const uint32_t qpt = L.tw / 4;
+  uint32_t mx = 0;
+  for (unsigned long long w = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; w < nwork;
+       w += (unsigned long long)gridDim.x * blockDim.x) {
+    const uint32_t kg = (uint32_t)(w % k16_total);
+    const unsigned long long qi = w / k16_total;
+    const uint32_t yl = (uint32_t)(qi / nxq), xq = (uint32_t)(qi - (unsigned long long)yl * nxq);
+    uint32_t v[16][4];
+    const uint32_t j0 = kg * 16;
+    if (yl < L.ny) {
+      const int32_t* t = L.base + ((size_t)yl * L.ntx + xq / qpt) * L.tile_stride + 4 * (xq % qpt);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        int4 d = make_int4(0, 0, 0, 0);
+        if (j0 + i < L.cap) d = __ldg(reinterpret_cast<const int4*>(t + (size_t)(j0 + i) * L.tw));
+        v[i][0] = (uint32_t)d.x; v[i][1] = (uint32_t)d.y; v[i][2] = (uint32_t)d.z; v[i][3] = (uint32_t)d.w;
+        mx = max(mx, max(max(v[i][0], v[i][1]), max(v[i][2], v[i][3])));
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i][0] = v[i][1] = v[i][2] = v[i][3] = 0;
+    }
+    const uint32_t nt = (uint32_t)(qi / 32), ql = (uint32_t)(qi % 32);   // cell tile, quad inside it
+    const uint32_t kc = kg / (DENSE_KC / 16), k16 = kg % (DENSE_KC / 16);
+    for (uint32_t q = 0; q < Q; ++q) {
+      uint8_t* dst = bop + ((((size_t)nt * nkc + kc) * Q + q) * (DENSE_KC / 16) + k16) * 2048 + (size_t)ql * 64;   // 4 rows x 16 B
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        uint32_t wds[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          wds[k] = ((v[4 * k][e] >> (8 * q)) & 255u) | (((v[4 * k + 1][e] >> (8 * q)) & 255u) << 8) |
+                   (((v[4 * k + 2][e] >> (8 * q)) & 255u) << 16) | (((v[4 * k + 3][e] >> (8 * q)) & 255u) << 24);
+        *reinterpret_cast<uint4*>(dst + 16 * e) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+      }
+    }
+  }
+  mx = __reduce_max_sync(FULL, mx);
+  if ((threadIdx.x & 31u) == 0 && mx) atomicMax(maxn, mx);
+}
+
+// ---- the fused dense generate kernel -----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const DenseParams p) {
+  extern __shared__ __align__(1024) unsigned char dense_smem[];
+  __shared__ uint64_t s_full[8], s_empty[8], s_tfull, s_tempty;
+  __shared__ uint32_t s_tmem;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t S = p.nstages, P = p.P, Q = p.Q;
+  const uint32_t a_bytes = P * DENSE_TILE_BYTES, b_bytes = Q * DENSE_TILE_BYTES, stage_bytes = a_bytes + b_bytes;
+  const uint32_t ntile_ids = ((p.mtiles + p.mblock - 1) / p.mblock) * p.mblock * p.ntn;
+
+  if (threadIdx.x == 0) {
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(s_full + s, 1); mbar_init(s_empty + s, 1); }
+    mbar_init(&s_tfull, 1);
+    mbar_init(&s_tempty, DENSE_EPI_WARPS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp == 0) {
+    // ===================== producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, round = 0;
+      for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
+        uint32_t mt, nt;
+        if (!dense_tile(p, id, mt, nt)) continue;
+        const uint8_t* a = p.aop + (size_t)mt * p.nkc * a_bytes;
+        const uint8_t* b = p.bop + (size_t)nt * p.nkc * b_bytes;
+        for (uint32_t kc = 0; kc < p.nkc; ++kc) {
+          if (round) mbar_wait_wd(s_empty + stage, (round - 1u) & 1u);
+          unsigned char* dst = dense_smem + (size_t)stage * stage_bytes;
+          mbar_expect_tx(s_full + stage, stage_bytes);
+          bulk_g2s(dst, a + (size_t)kc * a_bytes, a_bytes, s_full + stage);
+          bulk_g2s(dst + a_bytes, b + (size_t)kc * b_bytes, b_bytes, s_full + stage);
+          if (++stage == S) { stage = 0; ++round; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      // instruction descriptor: D s32 [4,6)=2, A s8 [7,10)=1, B u8 [10,13)=0, K-major both, N=128 -> 16 at [17,23), M=128 -> 8 at [24,29)
+      const uint32_t idesc = (2u << 4) | (1u << 7) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+      uint32_t stage = 0, round = 0, k = 0;
+      for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
+        uint32_t mt, nt;
+        if (!dense_tile(p, id, mt, nt)) continue;
+        if (k) mbar_wait_wd(&s_tempty, (k - 1u) & 1u);   // the epilogue has drained the accumulators of the previous tile
+        tc_fence_after();
+        uint32_t written = 0;                             // groups that already hold a partial sum of this tile
+        for (uint32_t kc = 0; kc < p.nkc; ++kc) {
+          mbar_wait_wd(s_full + stage, round & 1u);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(dense_smem + (size_t)stage * stage_bytes), sb = sa + a_bytes;
+          for (uint32_t pp = 0; pp < P; ++pp)
+            for (uint32_t q = 0; q < Q; ++q) {
+              const uint32_t g = q + (P - 1u) - pp;
+              if (g < p.g0 || g >= p.g1) continue;
+              const uint32_t col = (g - p.g0) * 128u;
+#pragma unroll
+              for (uint32_t kk = 0; kk < DENSE_KC / 32; ++kk) {
+                umma_i8(tmem + col, umma_desc(sa + pp * DENSE_TILE_BYTES + kk * 4096u), umma_desc(sb + q * DENSE_TILE_BYTES + kk * 4096u),
+                        idesc, (written >> g) & 1u);
+                written |= 1u << g;
+              }
+            }
+          umma_commit(s_empty + stage);                   // stage reusable once these MMAs have read it
+          if (++stage == S) { stage = 0; ++round; }
+        }
+        umma_commit(&s_tfull);                            // accumulators complete
+        ++k;
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9; TMEM lanes 32*(warp%4).., columns 64*((warp-2)/4)..) =====================
+    const uint32_t lq = warp & 3u, row = lq * 32u + lane, cbase = ((warp - 2u) >> 2) * 64u;
+    const uint32_t ngr = p.g1 - p.g0, qpt = p.L.tw / 4;
+    const double w0 = p.w0;
+    const bool final_round = !(p.flags & 2u);
+    uint32_t k = 0;
+    for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
+      uint32_t mt, nt;
+      if (!dense_tile(p, id, mt, nt)) continue;
+      const uint32_t sp = mt * 128u + row;
+      const double diag = p.diag[sp], rr = p.rr[sp], rs = p.rscale[sp];
+      double* part = p.partial ? p.partial + ((size_t)nt * p.mtiles + mt) * (128 * 128) + row : nullptr;
+      const bool live = final_round && sp < p.L.nsp;
+      // address of this thread's 4 densities of quad `qi` of the tile (null: padding)
+      auto quad_ptr = [&](uint32_t col) -> int32_t* {
+        const unsigned long long qi = (unsigned long long)nt * 32u + (col >> 2);
+        const uint32_t yl = (uint32_t)(qi / p.nxq), xq = (uint32_t)(qi - (unsigned long long)yl * p.nxq);
+        if (!live || yl >= p.L.ny) return nullptr;
+        return p.L.base + ((size_t)yl * p.L.ntx + xq / qpt) * p.L.tile_stride + (size_t)sp * p.L.tw + 4 * (xq % qpt);
+      };
+      int4 own[4], nxt[4];
+#pragma unroll
+      for (uint32_t qd = 0; qd < 4; ++qd) {
+        const int32_t* gp = quad_ptr(cbase + 4 * qd);
+        nxt[qd] = gp ? *reinterpret_cast<const int4*>(gp) : make_int4(0, 0, 0, 0);
+      }
+      mbar_wait_wd(&s_tfull, k & 1u);
+      tc_fence_after();
+      for (uint32_t c0 = cbase; c0 < cbase + 64; c0 += 16) {
+#pragma unroll
+        for (uint32_t qd = 0; qd < 4; ++qd) own[qd] = nxt[qd];
+        if (c0 + 16 < cbase + 64) {
+#pragma unroll
+          for (uint32_t qd = 0; qd < 4; ++qd) {
+            const int32_t* gp = quad_ptr(c0 + 16 + 4 * qd);
+            nxt[qd] = gp ? *reinterpret_cast<const int4*>(gp) : make_int4(0, 0, 0, 0);
+          }
+        }
+        int acc[DENSE_MAX_GROUPS][16];
+#pragma unroll
+        for (uint32_t g = 0; g < DENSE_MAX_GROUPS; ++g)
+          if (g < ngr) tmem_ld16(tmem + ((lq * 32u) << 16) + g * 128u + c0, acc[g]);
+#pragma unroll
+        for (uint32_t qd = 0; qd < 4; ++qd) {
+          double sum[4];
+#pragma unroll
+          for (uint32_t e = 0; e < 4; ++e) {
+            double t = 0.0;
+#pragma unroll
+            for (int g = DENSE_MAX_GROUPS - 1; g >= 0; --g)
+              if ((uint32_t)g < ngr) t = __dadd_rn(__dmul_rn(t, 256.0), (double)acc[g][4 * qd + e]);
+            t = __dmul_rn(t, w0);
+            if (p.flags & 1u) t = __dadd_rn(t, part[(size_t)(c0 + 4 * qd + e) * 128]);
+            sum[e] = t;
+          }
+          if (!final_round) {
+#pragma unroll
+            for (uint32_t e = 0; e < 4; ++e) part[(size_t)(c0 + 4 * qd + e) * 128] = sum[e];
+            continue;
+          }
+          int32_t* gp = quad_ptr(c0 + 4 * qd);
+          if (!gp) continue;
+          const unsigned long long qi = (unsigned long long)nt * 32u + ((c0 + 4 * qd) >> 2);
+          const uint32_t yl = (uint32_t)(qi / p.nxq), xq = (uint32_t)(qi - (unsigned long long)yl * p.nxq);
+          const int4 o4 = own[qd];
+          const double d[4] = {(double)(uint32_t)o4.x, (double)(uint32_t)o4.y, (double)(uint32_t)o4.z, (double)(uint32_t)o4.w};
+          double x[4];
+#pragma unroll
+          for (uint32_t e = 0; e < 4; ++e) {
+            const double ir = __dadd_rn(__dmul_rn(diag, d[e]), __dmul_rn(sum[e], rs));
+            x[e] = __dadd_rn(d[e], __dmul_rn(d[e], __dadd_rn(rr, ir)));
+          }
+          if (p.xout) {
+#pragma unroll
+            for (uint32_t e = 0; e < 4; ++e) {
+              const uint32_t xc = xq * 4 + e;
+              if (xc < p.L.nx) p.xout[((size_t)yl * p.L.nx + xc) * p.L.nsp + sp] = x[e];
+            }
+            continue;
+          }
+          const uint4 u = philox_rk(xq, p.L.y0 + yl, sp, (uint32_t)p.t0, p.rk);
+          int4 o;
+          o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
+          o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
+          *reinterpret_cast<int4*>(gp) = o;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_tempty);
+      ++k;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u));
+  }
+}
+
+}  // namespace eco

@@ -571,6 +571,9 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "maxNbrs") *out = (double)m->maxNbrs;
   else if (s == "launches") *out = (double)m->eng.launches();
   else if (s == "device_bytes") *out = (double)m->eng.bytes_allocated();
+  else if (s == "dense_active") *out = m->eng.dense_wanted() ? 1.0 : 0.0;
+  else if (s == "dense_q") *out = (double)m->eng.dense_last_q();
+  else if (s == "dense_macs") *out = (double)m->eng.dense_mma_per_step();
   else if (s == "nprocs") *out = (double)m->nprocs;
   else throw std::runtime_error("unknown scalar member: " + s);
   ECO_CATCH
@@ -967,6 +970,11 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   else if (k == "mig_variant") m->eng.mig_variant = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
   else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;
+  else if (k == "gen_dense") m->eng.gen_dense = value;
+  else if (k == "dense_slices") {
+    if (value < 1 || value > 7) throw std::runtime_error("dense_slices must be 1..7");
+    m->eng.dense_slices = value;
+  }
   else throw std::runtime_error("unknown tuning knob: " + k);
   ECO_CATCH
 }

@@ -241,7 +241,7 @@ class EcolabModelBase:
         a = np.zeros(16, dtype=np.float64)
         n = C.c_size_t()
         check(self._L.eco_kernel_times(self._h, _ptr(a), a.size, C.byref(n)))
-        names = ("generate", "migrate", "step")
+        names = ("generate", "migrate", "step", "dense_pack", "dense_mma")
         return {names[i]: (a[2 * i], int(a[2 * i + 1])) for i in range(n.value // 2)}
 
     # ---- the reflected methods ---------------------------------------------------
