@@ -329,6 +329,98 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
                     else "eco_set_density_all + eco_step + eco_get_density_all"}
 
 
+def run_dense(args):
+    """BASELINE.json config 5: 256 x 256 cells x 8192 species, beta fully dense -- generate on the tensor cores
+    (tcgen05 kind::i8 slices, ecolab_b200/csrc/k_dense.cuh) + migrate, and the FP64 sparse kernel on the same model."""
+    import torch
+    import ecolab_b200 as E
+    import ctypes as C
+    from helpers import SCALARS
+    torch.cuda.set_device(0)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    nx, ny, nsp = args.nx or 256, args.ny or 256, args.nsp if args.nsp != 1024 else 8192
+    rng = np.random.default_rng(10)
+    m = E.SpatialModel(0, None)
+    E._cabi.check(m._L.eco_set_stream(m._h, C.c_void_p(stream.cuda_stream)))
+    for k, v in SCALARS.items():
+        getattr(m, k)(v)
+    m.species(np.arange(nsp, dtype=np.int32))
+    m.repro_rate(rng.uniform(-0.1, 0.1, nsp))
+    m.interaction.diag(np.full(nsp, -1e-3))
+    idx = np.arange(nsp, dtype=np.uint32)
+    row = np.repeat(idx, nsp - 1)
+    col = np.tile(idx, nsp).reshape(nsp, nsp)[~np.eye(nsp, dtype=bool)].astype(np.uint32)
+    # 67 M entries: the plain array setter of the host mirror (the callable members also return the list they set)
+    m._set_array("interaction.row", "u32", row); m._set_array("interaction.col", "u32", col)
+    m._set_array("interaction.val", "f64", rng.uniform(-1e-5, 1e-5, row.size))
+    del row, col
+    m.mutation(np.full(nsp, 1e-5)); m.migration(np.full(nsp, 0.1)); m.create(np.zeros(nsp))
+    m.setGrid(nx, ny)
+    m.seed(10)
+    if args.dense_slices:
+        m.set_tuning("dense_slices", args.dense_slices)
+    m.fill_density_random(0, 199)
+    updates = nx * ny * nsp
+    if args.dense_prof:
+        m._scalar("dense_prof0")     # enables the in-kernel cycle counters
+    for _ in range(args.warmup):
+        m.step(1)
+    assert m._scalar("dense_active") == 1
+    m.set_tuning("timing", 1)
+    torch.cuda.synchronize()
+    l0 = m.launches()
+    sampler = ClockSampler(0); sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        m.step(1)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    kt = m.kernel_times()
+    m.set_tuning("timing", 0)
+    launches = m.launches() - l0
+    macs, q = m._scalar("dense_macs"), int(m._scalar("dense_q"))
+    mma_ms = kt["dense_mma"][0] / max(kt["dense_mma"][1], 1)
+    pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    bf16 = float(pk.get("bf16_tflops_sustained", 1400.0))
+    peak = 2.0 * bf16      # int8 tensor rate = 2 x bf16 (nominal 4.5 vs 2.25 POP/s); measured bf16 sustained x 2
+    launches_per_step = kt["dense_mma"][1] / args.steps
+    achieved = 2.0 * macs / (mma_ms * launches_per_step * 1e-3) / 1e12
+    roofline = {"bound": "tensor", "kernel": "generate_dense_kernel", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)",
+                "frac": achieved / peak, "traffic": None,
+                "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops_sustained (int8 = 2 x bf16 rate; of measured)" if pk else "fallback",
+                "executed_int8_macs_per_step": macs, "beta_slices": int(args.dense_slices or 3), "density_slices": q,
+                "algorithmic_tflops": 2.0 * nsp * updates / (mma_ms * launches_per_step * 1e-3) / 1e12,
+                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]}}
+    # the FP64 sparse kernel on the same dense model (config 5: "tcgen05 contraction path vs sparse path")
+    sparse_ms = None
+    if not args.no_cpu:
+        try:
+            m.set_tuning("gen_dense", -1)
+            m.generate(1)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream); m.generate(1); b.record(stream)
+            torch.cuda.synchronize()
+            sparse_ms = a.elapsed_time(b)
+        except Exception as ex:   # noqa: BLE001
+            sparse_ms = f"unavailable: {ex}"
+    if args.dense_prof:
+        names = ("mma_wait_tmem_empty", "mma_wait_smem_full", "mma_issue", "tiles", "epi_wait_tmem_full", "epi_work")
+        roofline["cta0_cycles_last_launch"] = {n: int(m._scalar(f"dense_prof{i}")) for i, n in enumerate(names)}
+    line = {"metric": METRIC, "value": updates * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "s8 x u8 -> s32 slices, f64 epilogue -> i32", "data": "synthetic",
+            "config": {"workload": f"dense-interaction stress: spatial {nx}x{ny} cells x {nsp} species, beta fully dense, generate(1)+migrate() per step",
+                       "l2": "inputs (%.1f GiB) larger than L2" % (updates * 4 / 2**30)},
+            "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline,
+            "sparse_fp64_generate_ms": sparse_ms, "dense_generate_ms": (kt["dense_mma"][0] + kt["dense_pack"][0]) / args.steps}
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -347,10 +439,15 @@ def main():
     ap.add_argument("--e2e-unpipelined", action="store_true", dest="e2e_unpipelined")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dense", action="store_true", help="config 5: 256x256x8192, dense beta, tensor-core generate")
+    ap.add_argument("--dense-slices", type=int, default=0, dest="dense_slices")
+    ap.add_argument("--dense-prof", action="store_true", dest="dense_prof")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif args.dense:
+        run_dense(args)
     else:
         run_native(args)
 

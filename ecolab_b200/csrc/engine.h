@@ -127,6 +127,7 @@ class Engine {
   int gen_dense = 0;
   int dense_slices = 3;
   bool dense_wanted() const;
+  void dense_profile(unsigned long long* out8);   // enables the in-kernel cycle counters; returns CTA 0's of the last launch
   uint32_t dense_last_q() const { return dense_q_; }        // density slices used by the last dense generate
   uint64_t dense_mma_per_step() const { return dense_macs_; }   // integer MACs issued by the last dense generate step
 
@@ -172,6 +173,7 @@ class Engine {
   unsigned int* d_maxn_ = nullptr; unsigned int* h_maxn_ = nullptr;
   uint32_t dense_p_ = 0, dense_nsp_ = 0, dense_mtiles_ = 0, dense_nkc_ = 0, dense_q_ = 1;
   uint64_t dense_macs_ = 0;
+  unsigned long long* dense_prof_ = nullptr;
   uint64_t beta_version_ = 0, dense_version_ = ~0ull;
 
   // scratch

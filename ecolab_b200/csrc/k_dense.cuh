@@ -16,10 +16,11 @@
 // is why the sparse kernel stays the default and this path is selected only for dense beta (Engine::dense_wanted).
 //
 // Operands live in HBM as ready-made shared-memory images, so a pipeline stage is filled by two 1-D bulk copies
-// (TMA unit, SASS UBLKCP) and needs no tensor map: un-swizzled K-major "core matrix" layout
-//     tile[k16 = KC/16][row group = 16][row = 8][16 bytes]       (128 rows x KC bytes of K)
-// for which the tcgen05 shared-memory descriptor is  LBO = 2048 (stride between 16-byte K chunks), SBO = 128
-// (stride between 8-row groups) -- pinned on B200 by tools/umma_probe.cu (profiles/r1_umma_probe.txt).
+// (TMA unit, SASS UBLKCP) and needs no tensor map: K-major tiles of 128 rows x 128 bytes of K in the 128-byte swizzle
+//     tile[row group = 16][row = 8][128 bytes],  16-byte chunk c of row r stored at chunk position c ^ (r % 8)
+// for which the tcgen05 shared-memory descriptor is layout SWIZZLE_128B, SBO = 1024 (stride between 8-row groups), and a
+// K step of 32 bytes advances the start address by 32 -- pinned on B200 by tools/umma_probe.cu
+// (profiles/r1_umma_probe.txt).  Q = 2 density slices sit back to back and are multiplied as ONE N = 256 operand.
 //     A: [m_tile][kc][p]  -> P consecutive tiles = one bulk copy        (built once per beta upload, host side)
 //     B: [n_tile][kc][q]  -> Q consecutive tiles = one bulk copy        (dense_pack_kernel, every timestep)
 // N runs over the padded cell quads of the slab in (row, x) order: N index = 4*(yl*nxq + xq) + e.
@@ -36,7 +37,7 @@
 
 namespace eco {
 
-constexpr uint32_t DENSE_KC = 64;                    // K bytes (species) per pipeline stage and operand tile
+constexpr uint32_t DENSE_KC = 128;                   // K bytes (species) per pipeline stage and operand tile
 constexpr uint32_t DENSE_TILE_BYTES = 128 * DENSE_KC;   // one 128-row operand tile
 constexpr uint32_t DENSE_MAX_GROUPS = 4;             // 4 accumulators x 128 columns = the 512 TMEM columns
 constexpr uint32_t DENSE_EPI_WARPS = 8;               // two per TMEM lane quadrant, 64 accumulator columns each
@@ -50,6 +51,7 @@ struct DenseParams {
   const double* rr;            // [mtiles*128] repro_rate
   const double* rscale;        // [mtiles*128] 2^-s_i
   double* partial;             // [ntn][mtiles][128 cols][128 rows] running sums between group rounds, or null
+  unsigned long long* prof;    // optional [grid][8] cycle counters (tools only): MMA warp waits / issue, epilogue wait / work
   double* xout;                // cell-major [cell][nsp] pre-rounding x (diagnostic), or null
   uint32_t P, Q;               // slices of beta / of the densities
   uint32_t g0, g1;             // groups [g0, g1) handled by this launch (g1 - g0 <= 4)
@@ -64,9 +66,10 @@ struct DenseParams {
 };
 
 // ---- tcgen05 wrappers ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {   // LBO 2048 B, SBO 128 B, version 1, no swizzle
-  return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)(2048u >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
-}
+// SWIZZLE_128B K-major descriptor: start address >> 4 in [0,14), LBO field 1 (unused for swizzled K-major), SBO = 1024 B
+// in [32,46), version 1 in [46,48), layout type 2 in [61,64).  `lo` = (shared address >> 4) | 1 << 16.
+constexpr uint32_t UMMA_DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint64_t umma_desc(uint32_t lo) { return ((uint64_t)UMMA_DESC_HI << 32) | lo; }
 __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
                "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
@@ -111,6 +114,33 @@ __device__ __forceinline__ bool dense_tile(const DenseParams& p, uint32_t id, ui
   return mt < p.mtiles;
 }
 
+// ---- MMA issue of one pipeline stage, everything but the two base addresses known at compile time ------------------------
+// A single thread issues the MMAs, so the tensor pipe runs only as fast as that thread gets through its instructions
+// (measured: 64 cycles per M128 x N128 x 32 B MMA with a bare issue loop, ~300 with run-time slice loops): slice counts
+// are template parameters, the accumulate flags and descriptor offsets fold to constants.  FIRST = first K step of a tile
+// (accumulators start from zero; the N = 256 stacking of two density slices cannot be used there because a 256-column
+// MMA has one accumulate flag for two groups that start at different moments).
+constexpr uint32_t DENSE_IDESC128 = (2u << 4) | (1u << 7) | ((128u >> 3) << 17) | ((128u >> 4) << 24);   // D s32, A s8, B u8, K-major
+constexpr uint32_t DENSE_IDESC256 = (2u << 4) | (1u << 7) | ((256u >> 3) << 17) | ((128u >> 4) << 24);
+template <int P, int Q, bool FIRST>
+__device__ __forceinline__ void dense_issue_stage(uint32_t tmem, uint32_t a_lo, uint32_t b_lo) {
+#pragma unroll
+  for (int ks = 0; ks < (int)(DENSE_KC / 32); ++ks) {
+#pragma unroll
+    for (int pp = 0; pp < P; ++pp) {
+      const uint64_t ad = umma_desc(a_lo + pp * (DENSE_TILE_BYTES >> 4) + ks * 2);
+      if (Q == 2 && !(FIRST && ks == 0)) {
+        umma_i8(tmem + (P - 1 - pp) * 128, ad, umma_desc(b_lo + ks * 2), DENSE_IDESC256, 1u);
+      } else {
+#pragma unroll
+        for (int q = 0; q < Q; ++q)   // group g = q + P-1-pp was touched before by (pp-1, q-1) when both exist
+          umma_i8(tmem + (q + P - 1 - pp) * 128, ad, umma_desc(b_lo + q * (DENSE_TILE_BYTES >> 4) + ks * 2), DENSE_IDESC128,
+                  (FIRST && ks == 0 && !(pp > 0 && q > 0)) ? 0u : 1u);
+      }
+    }
+  }
+}
+
 // ---- B operand: int32 densities -> Q u8 slices in the shared-memory image layout ---------------------------------------
 // One thread = 16 consecutive species x one cell quad: 16 LDG.128 (contiguous 256 B when TW = 4) -> 4*Q STG.128.
 __global__ void __launch_bounds__(256) dense_pack_kernel(const Layout L, uint8_t* __restrict__ bop, uint32_t Q, uint32_t nkc,
@@ -143,15 +173,17 @@ __global__ void __launch_bounds__(256) dense_pack_kernel(const Layout L, uint8_t
     const uint32_t nt = (uint32_t)(qi / 32), ql = (uint32_t)(qi % 32);   // cell tile, quad inside it
     const uint32_t kc = kg / (DENSE_KC / 16), k16 = kg % (DENSE_KC / 16);
     for (uint32_t q = 0; q < Q; ++q) {
-      uint8_t* dst = bop + ((((size_t)nt * nkc + kc) * Q + q) * (DENSE_KC / 16) + k16) * 2048 + (size_t)ql * 64;   // 4 rows x 16 B
+      // rows 4*ql .. 4*ql+3 of the tile; row r = 8*(r/8) + r%8 lives at (r/8)*1024 + (r%8)*128, its chunk k16 at (k16 ^ r%8)*16
+      uint8_t* dst = bop + (((size_t)nt * nkc + kc) * Q + q) * DENSE_TILE_BYTES + (size_t)(ql >> 1) * 1024;
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
+        const uint32_t r8 = (ql & 1u) * 4 + e;
         uint32_t wds[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           wds[k] = ((v[4 * k][e] >> (8 * q)) & 255u) | (((v[4 * k + 1][e] >> (8 * q)) & 255u) << 8) |
                    (((v[4 * k + 2][e] >> (8 * q)) & 255u) << 16) | (((v[4 * k + 3][e] >> (8 * q)) & 255u) << 24);
-        *reinterpret_cast<uint4*>(dst + 16 * e) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+        *reinterpret_cast<uint4*>(dst + r8 * 128 + ((k16 ^ r8) * 16)) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
       }
     }
   }
@@ -206,37 +238,52 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      // instruction descriptor: D s32 [4,6)=2, A s8 [7,10)=1, B u8 [10,13)=0, K-major both, N=128 -> 16 at [17,23), M=128 -> 8 at [24,29)
-      const uint32_t idesc = (2u << 4) | (1u << 7) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+      long long pc[3] = {0, 0, 0};
+      // single-round launches of the common slicings take the compile-time issue path
+      const uint32_t fast = (p.g0 == 0 && p.g1 == P + Q - 1u) ? P * 10u + Q : 0u;
       uint32_t stage = 0, round = 0, k = 0;
       for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
         uint32_t mt, nt;
         if (!dense_tile(p, id, mt, nt)) continue;
+        long long c0 = clock64();
         if (k) mbar_wait_wd(&s_tempty, (k - 1u) & 1u);   // the epilogue has drained the accumulators of the previous tile
         tc_fence_after();
+        pc[0] += clock64() - c0;
         uint32_t written = 0;                             // groups that already hold a partial sum of this tile
         for (uint32_t kc = 0; kc < p.nkc; ++kc) {
+          c0 = clock64();
           mbar_wait_wd(s_full + stage, round & 1u);
           tc_fence_after();
-          const uint32_t sa = smem_u32(dense_smem + (size_t)stage * stage_bytes), sb = sa + a_bytes;
-          for (uint32_t pp = 0; pp < P; ++pp)
-            for (uint32_t q = 0; q < Q; ++q) {
-              const uint32_t g = q + (P - 1u) - pp;
-              if (g < p.g0 || g >= p.g1) continue;
-              const uint32_t col = (g - p.g0) * 128u;
+          const long long c1 = clock64();
+          pc[1] += c1 - c0;
+          const uint32_t sa = smem_u32(dense_smem + (size_t)stage * stage_bytes);
+          const uint32_t a_lo = (sa >> 4) | (1u << 16), b_lo = ((sa + a_bytes) >> 4) | (1u << 16);
+          if (fast == 31u) { if (kc) dense_issue_stage<3, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<3, 1, true>(tmem, a_lo, b_lo); }
+          else if (fast == 32u) { if (kc) dense_issue_stage<3, 2, false>(tmem, a_lo, b_lo); else dense_issue_stage<3, 2, true>(tmem, a_lo, b_lo); }
+          else if (fast == 21u) { if (kc) dense_issue_stage<2, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<2, 1, true>(tmem, a_lo, b_lo); }
+          else if (fast == 22u) { if (kc) dense_issue_stage<2, 2, false>(tmem, a_lo, b_lo); else dense_issue_stage<2, 2, true>(tmem, a_lo, b_lo); }
+          else if (fast == 41u) { if (kc) dense_issue_stage<4, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<4, 1, true>(tmem, a_lo, b_lo); }
+          else {
+            // any other slicing / a multi-round launch: run-time loops (correct, slower to issue)
 #pragma unroll
-              for (uint32_t kk = 0; kk < DENSE_KC / 32; ++kk) {
-                umma_i8(tmem + col, umma_desc(sa + pp * DENSE_TILE_BYTES + kk * 4096u), umma_desc(sb + q * DENSE_TILE_BYTES + kk * 4096u),
-                        idesc, (written >> g) & 1u);
-                written |= 1u << g;
-              }
-            }
+            for (uint32_t ks = 0; ks < DENSE_KC / 32; ++ks)
+              for (uint32_t pp = 0; pp < P; ++pp)
+                for (uint32_t q = 0; q < Q; ++q) {
+                  const uint32_t g = q + (P - 1u) - pp;
+                  if (g < p.g0 || g >= p.g1) continue;
+                  umma_i8(tmem + (g - p.g0) * 128u, umma_desc(a_lo + pp * (DENSE_TILE_BYTES >> 4) + ks * 2u),
+                          umma_desc(b_lo + q * (DENSE_TILE_BYTES >> 4) + ks * 2u), DENSE_IDESC128, (written >> g) & 1u);
+                  written |= 1u << g;
+                }
+          }
           umma_commit(s_empty + stage);                   // stage reusable once these MMAs have read it
+          pc[2] += clock64() - c1;
           if (++stage == S) { stage = 0; ++round; }
         }
         umma_commit(&s_tfull);                            // accumulators complete
         ++k;
       }
+      if (p.prof) { p.prof[blockIdx.x * 8 + 0] = pc[0]; p.prof[blockIdx.x * 8 + 1] = pc[1]; p.prof[blockIdx.x * 8 + 2] = pc[2]; p.prof[blockIdx.x * 8 + 3] = k; }
     }
   } else {
     // ===================== epilogue (warps 2..9; TMEM lanes 32*(warp%4).., columns 64*((warp-2)/4)..) =====================
@@ -244,6 +291,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     const uint32_t ngr = p.g1 - p.g0, qpt = p.L.tw / 4;
     const double w0 = p.w0;
     const bool final_round = !(p.flags & 2u);
+    long long ew = 0, ex = 0;
     uint32_t k = 0;
     for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
       uint32_t mt, nt;
@@ -265,8 +313,12 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
         const int32_t* gp = quad_ptr(cbase + 4 * qd);
         nxt[qd] = gp ? *reinterpret_cast<const int4*>(gp) : make_int4(0, 0, 0, 0);
       }
+      const long long e0 = clock64();
       mbar_wait_wd(&s_tfull, k & 1u);
       tc_fence_after();
+      const long long e1 = clock64();
+      ew += e1 - e0;
+#pragma unroll 1
       for (uint32_t c0 = cbase; c0 < cbase + 64; c0 += 16) {
 #pragma unroll
         for (uint32_t qd = 0; qd < 4; ++qd) own[qd] = nxt[qd];
@@ -329,8 +381,10 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_tempty);
+      ex += clock64() - e1;
       ++k;
     }
+    if (p.prof && warp == 2 && lane == 0) { p.prof[blockIdx.x * 8 + 4] = ew; p.prof[blockIdx.x * 8 + 5] = ex; }
   }
 
   tc_fence_before();

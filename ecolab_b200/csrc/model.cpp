@@ -574,6 +574,11 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "dense_active") *out = m->eng.dense_wanted() ? 1.0 : 0.0;
   else if (s == "dense_q") *out = (double)m->eng.dense_last_q();
   else if (s == "dense_macs") *out = (double)m->eng.dense_mma_per_step();
+  else if (s.rfind("dense_prof", 0) == 0) {   // dense_prof0..7: in-kernel cycle counters of CTA 0 (first call enables them)
+    unsigned long long v[8];
+    m->eng.dense_profile(v);
+    *out = (double)v[std::min(7, std::max(0, s.size() > 10 ? s[10] - '0' : 0))];
+  }
   else if (s == "nprocs") *out = (double)m->nprocs;
   else throw std::runtime_error("unknown scalar member: " + s);
   ECO_CATCH

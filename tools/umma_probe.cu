@@ -15,16 +15,17 @@
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t layout_type = 0) {
   return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) |
-         (1ull << 46);
+         (1ull << 46) | ((uint64_t)layout_type << 61);
 }
 
 // KIND 0: i8 (A signed, B unsigned, D s32)   KIND 1: bf16 x bf16 -> f32
 template <int KIND>
 __global__ void __launch_bounds__(128, 1) probe_kernel(const uint8_t* __restrict__ a_img, const uint8_t* __restrict__ b_img,
                                                        uint32_t* __restrict__ out, uint32_t kbytes, uint32_t lbo_a, uint32_t sbo_a,
-                                                       uint32_t lbo_b, uint32_t sbo_b, uint32_t idesc, uint32_t N) {
+                                                       uint32_t lbo_b, uint32_t sbo_b, uint32_t idesc, uint32_t N, uint32_t sw128,
+                                                       uint32_t nrep, long long* cycles) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t s_tmem;
@@ -46,21 +47,35 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(const uint8_t* __restrict
   asm volatile("tcgen05.fence::after_thread_sync;");
   const uint32_t tmem = s_tmem;
   if (threadIdx.x == 0) {
-    const uint32_t nk = kbytes / 32;
-    for (uint32_t k = 0; k < nk; ++k) {
-      const uint64_t ad = make_desc(smem_u32(sa) + k * 2 * 128 * 16, lbo_a, sbo_a);   // 2 k16 chunks per MMA
-      const uint64_t bd = make_desc(smem_u32(sb) + k * 2 * N * 16, lbo_b, sbo_b);
-      const uint32_t acc = k ? 1u : 0u;
-      if (KIND == 0)
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem),
-                     "l"(ad), "l"(bd), "r"(idesc), "r"(acc)
-                     : "memory");
-      else
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem),
-                     "l"(ad), "l"(bd), "r"(idesc), "r"(acc)
-                     : "memory");
+    // descriptors of the 4 K steps, built once: the timed loop is nothing but the MMA issue
+    uint64_t ad[4], bd[4];
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+      // un-swizzled: 2 k16 chunks per MMA, a chunk is rows*16 bytes away; 128B swizzle: K runs inside the 128-byte row
+      ad[k] = sw128 ? make_desc(smem_u32(sa) + k * 32, 16, 1024, 2) : make_desc(smem_u32(sa) + k * 2 * 128 * 16, lbo_a, sbo_a);
+      bd[k] = sw128 ? make_desc(smem_u32(sb) + k * 32, 16, 1024, 2) : make_desc(smem_u32(sb) + k * 2 * N * 16, lbo_b, sbo_b);
+    }
+    const long long t0 = clock64();
+    for (uint32_t rep = 0; rep < nrep; ++rep) {
+#pragma unroll
+      for (uint32_t k = 0; k < 4; ++k) {
+        const uint32_t acc = (k || rep) ? 1u : 0u;
+        if (KIND == 0)
+          asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem),
+                       "l"(ad[k]), "l"(bd[k]), "r"(idesc), "r"(acc)
+                       : "memory");
+        else
+          asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem),
+                       "l"(ad[k]), "l"(bd[k]), "r"(idesc), "r"(acc)
+                       : "memory");
+      }
     }
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+    uint32_t ok = 0;
+    for (uint32_t spin = 0; spin < (1u << 24) && !ok; ++spin)
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                   : "=r"(ok) : "r"(smem_u32(&bar)), "r"(0u) : "memory");
+    if (cycles) *cycles = clock64() - t0;
   }
   // bounded wait: a wrong descriptor must not hang the box
   uint32_t done = 0;
@@ -91,14 +106,19 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(const uint8_t* __restrict
 }
 
 // canonical un-swizzled K-major image: [k16][row group of 8][8 rows][16 bytes]
+static bool g_sw128 = false;
 static size_t img_off(uint32_t rows, uint32_t r, uint32_t kbyte) {
+  // 128-byte swizzle (Swizzle<3,4,3>): atoms of 8 rows x 128 B, 16-byte chunk index XOR row-in-atom; K extent = 128 B
+  if (g_sw128) return (size_t)(r / 8) * 1024 + (r % 8) * 128 + (((kbyte / 16) ^ (r % 8)) * 16) + kbyte % 16;
   return (size_t)(kbyte / 16) * rows * 16 + (size_t)(r / 8) * 128 + (r % 8) * 16 + kbyte % 16;
 }
 
 int main() {
   const uint32_t M = 128, KB = 128;
   int fails = 0;
+  for (int sw = 0; sw < 2; ++sw)
   for (uint32_t N : {128u, 64u, 256u}) {
+    g_sw128 = sw != 0;
     for (int kind = 0; kind < 2; ++kind) {
       std::vector<uint8_t> a(M * KB), b(N * KB);
       std::vector<int8_t> A(M * KB);
@@ -132,7 +152,8 @@ int main() {
         const size_t smem = (size_t)(M + N) * KB;
         auto kern = kind == 0 ? probe_kernel<0> : probe_kernel<1>;
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<1, 128, smem>>>(da, db, dout, KB, v.la, v.sa, v.lb, v.sb, idesc, N);
+        long long* dcyc; CK(cudaMalloc(&dcyc, 8)); CK(cudaMemset(dcyc, 0, 8));
+        kern<<<1, 128, smem>>>(da, db, dout, KB, v.la, v.sa, v.lb, v.sb, idesc, N, (uint32_t)sw, 1u, dcyc);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("kind %d N %u variant '%s': CUDA error %s\n", kind, N, v.name, cudaGetErrorString(e)); return 3; }
         std::vector<uint32_t> out(M * N);
@@ -152,8 +173,12 @@ int main() {
               bad += got != ref;
             }
           }
-        printf("kind %s N %3u variant '%s': %s (%zu / %u mismatches)\n", kind == 0 ? "i8 " : "f16", N, v.name,
-               timeout ? "TIMEOUT" : bad ? "WRONG" : "OK", bad, M * N);
+        // throughput: 512 back-to-back repetitions of the 4 k-steps on the same operands
+        kern<<<1, 128, smem>>>(da, db, dout, KB, v.la, v.sa, v.lb, v.sb, idesc, N, (uint32_t)sw, 512u, dcyc);
+        CK(cudaDeviceSynchronize());
+        long long cyc = 0; CK(cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost)); cudaFree(dcyc);
+        printf("kind %s N %3u layout %s: %s (%zu / %u mismatches)  %.1f cycles per MMA (M128 x N%u x 32 B)\n", kind == 0 ? "i8 " : "f16", N,
+               sw ? "SWIZZLE_128B" : "un-swizzled ", timeout ? "TIMEOUT" : bad ? "WRONG" : "OK", bad, M * N, (double)cyc / (512.0 * 4), N);
         if (&v == &variants[0] && (timeout || bad)) ++fails;
       }
       cudaFree(da); cudaFree(db); cudaFree(dout);
