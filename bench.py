@@ -360,7 +360,7 @@ def run_dense(args):
     m.seed(10)
     if args.dense_slices:
         m.set_tuning("dense_slices", args.dense_slices)
-    m.fill_density_random(0, 199)
+    m.fill_density_random(0, args.dense_dmax)   # < 256: one u8 slice per density; larger: two
     updates = nx * ny * nsp
     if args.dense_prof:
         m._scalar("dense_prof0")     # enables the in-kernel cycle counters
@@ -442,6 +442,7 @@ def main():
     ap.add_argument("--dense", action="store_true", help="config 5: 256x256x8192, dense beta, tensor-core generate")
     ap.add_argument("--dense-slices", type=int, default=0, dest="dense_slices")
     ap.add_argument("--dense-prof", action="store_true", dest="dense_prof")
+    ap.add_argument("--dense-dmax", type=int, default=199, dest="dense_dmax")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     if args.impl == "reference":

@@ -40,7 +40,9 @@ namespace eco {
 constexpr uint32_t DENSE_KC = 128;                   // K bytes (species) per pipeline stage and operand tile
 constexpr uint32_t DENSE_TILE_BYTES = 128 * DENSE_KC;   // one 128-row operand tile
 constexpr uint32_t DENSE_MAX_GROUPS = 4;             // 4 accumulators x 128 columns = the 512 TMEM columns
-constexpr uint32_t DENSE_EPI_WARPS = 8;               // two per TMEM lane quadrant, 64 accumulator columns each
+constexpr uint32_t DENSE_EPI_WARPS = 16;              // four per TMEM lane quadrant, 32 accumulator columns each
+constexpr uint32_t DENSE_EPI_COLS = 128 / (DENSE_EPI_WARPS / 4);   // accumulator columns per epilogue warp
+constexpr uint32_t DENSE_CHUNK = 8;                   // columns per tcgen05.ld (2 cell quads)
 constexpr uint32_t DENSE_THREADS = (2 + DENSE_EPI_WARPS) * 32;
 
 struct DenseParams {
@@ -87,6 +89,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int (&v)[16]) {
       "tcgen05.wait::ld.sync.aligned;"   // same statement: no use of v[] can be scheduled before the wait
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
         "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int (&v)[8]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
       : "r"(taddr)
       : "memory");
 }
@@ -192,6 +203,9 @@ __global__ void __launch_bounds__(256) dense_pack_kernel(const Layout L, uint8_t
 }
 
 // ---- the fused dense generate kernel -----------------------------------------------------------------------------------
+// NGR = weight groups of this launch when it is a plain single-round launch (flags == 0): the recombination unrolls
+// without predicates; NGR = 0 is the general form (any group count, partial sums between rounds).
+template <int NGR>
 __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const DenseParams p) {
   extern __shared__ __align__(1024) unsigned char dense_smem[];
   __shared__ uint64_t s_full[8], s_empty[8], s_tfull, s_tempty;
@@ -287,12 +301,16 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     }
   } else {
     // ===================== epilogue (warps 2..9; TMEM lanes 32*(warp%4).., columns 64*((warp-2)/4)..) =====================
-    const uint32_t lq = warp & 3u, row = lq * 32u + lane, cbase = ((warp - 2u) >> 2) * 64u;
-    const uint32_t ngr = p.g1 - p.g0, qpt = p.L.tw / 4;
+    const uint32_t lq = warp & 3u, row = lq * 32u + lane, cbase = ((warp - 2u) >> 2) * DENSE_EPI_COLS;
+    const uint32_t ngr = NGR ? (uint32_t)NGR : p.g1 - p.g0;
+    const uint32_t qsh = p.L.tw == 4 ? 0u : p.L.tw == 8 ? 1u : p.L.tw == 16 ? 2u : 3u;   // log2(quads per density tile)
     const double w0 = p.w0;
-    const bool final_round = !(p.flags & 2u);
+    const bool final_round = NGR ? true : !(p.flags & 2u), add_partial = NGR ? false : (p.flags & 1u) != 0;
     long long ew = 0, ex = 0;
     uint32_t k = 0;
+    // a cursor walks the padded quads of the slab in (row, x) order; null pointer = nothing to update there
+    struct Cursor { uint32_t yl, xq; };
+    auto advance = [&](Cursor& c) { if (++c.xq == p.nxq) { c.xq = 0; ++c.yl; } };
     for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
       uint32_t mt, nt;
       if (!dense_tile(p, id, mt, nt)) continue;
@@ -300,61 +318,72 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
       const double diag = p.diag[sp], rr = p.rr[sp], rs = p.rscale[sp];
       double* part = p.partial ? p.partial + ((size_t)nt * p.mtiles + mt) * (128 * 128) + row : nullptr;
       const bool live = final_round && sp < p.L.nsp;
-      // address of this thread's 4 densities of quad `qi` of the tile (null: padding)
-      auto quad_ptr = [&](uint32_t col) -> int32_t* {
-        const unsigned long long qi = (unsigned long long)nt * 32u + (col >> 2);
-        const uint32_t yl = (uint32_t)(qi / p.nxq), xq = (uint32_t)(qi - (unsigned long long)yl * p.nxq);
-        if (!live || yl >= p.L.ny) return nullptr;
-        return p.L.base + ((size_t)yl * p.L.ntx + xq / qpt) * p.L.tile_stride + (size_t)sp * p.L.tw + 4 * (xq % qpt);
+      int32_t* const sp_base = p.L.base + (size_t)sp * p.L.tw;
+      auto quad_ptr = [&](const Cursor& c) -> int32_t* {
+        if (!live || c.yl >= p.L.ny) return nullptr;
+        return sp_base + ((size_t)c.yl * p.L.ntx + (c.xq >> qsh)) * p.L.tile_stride + 4u * (c.xq & ((1u << qsh) - 1u));
       };
-      int4 own[4], nxt[4];
+      const uint32_t q0 = nt * 32u + (cbase >> 2);   // first quad of this warp's columns
+      Cursor cw, cp;
+      cw.yl = q0 / p.nxq; cw.xq = q0 - cw.yl * p.nxq;
+      cp = cw;
+      constexpr uint32_t NQ = DENSE_CHUNK / 4;   // quads per chunk
+      int4 own[NQ], nxt[NQ];
 #pragma unroll
-      for (uint32_t qd = 0; qd < 4; ++qd) {
-        const int32_t* gp = quad_ptr(cbase + 4 * qd);
+      for (uint32_t qd = 0; qd < NQ; ++qd) {
+        const int32_t* gp = quad_ptr(cp);
         nxt[qd] = gp ? *reinterpret_cast<const int4*>(gp) : make_int4(0, 0, 0, 0);
+        advance(cp);
       }
       const long long e0 = clock64();
       mbar_wait_wd(&s_tfull, k & 1u);
       tc_fence_after();
       const long long e1 = clock64();
       ew += e1 - e0;
-#pragma unroll 1
-      for (uint32_t c0 = cbase; c0 < cbase + 64; c0 += 16) {
+#pragma unroll 2
+      for (uint32_t c0 = cbase; c0 < cbase + DENSE_EPI_COLS; c0 += DENSE_CHUNK) {
 #pragma unroll
-        for (uint32_t qd = 0; qd < 4; ++qd) own[qd] = nxt[qd];
-        if (c0 + 16 < cbase + 64) {
+        for (uint32_t qd = 0; qd < NQ; ++qd) own[qd] = nxt[qd];
+        if (c0 + DENSE_CHUNK < cbase + DENSE_EPI_COLS) {
 #pragma unroll
-          for (uint32_t qd = 0; qd < 4; ++qd) {
-            const int32_t* gp = quad_ptr(c0 + 16 + 4 * qd);
+          for (uint32_t qd = 0; qd < NQ; ++qd) {
+            const int32_t* gp = quad_ptr(cp);
             nxt[qd] = gp ? *reinterpret_cast<const int4*>(gp) : make_int4(0, 0, 0, 0);
+            advance(cp);
           }
         }
-        int acc[DENSE_MAX_GROUPS][16];
+        int acc[DENSE_MAX_GROUPS][DENSE_CHUNK];
 #pragma unroll
         for (uint32_t g = 0; g < DENSE_MAX_GROUPS; ++g)
-          if (g < ngr) tmem_ld16(tmem + ((lq * 32u) << 16) + g * 128u + c0, acc[g]);
+          if (g < ngr) tmem_ld8(tmem + ((lq * 32u) << 16) + g * 128u + c0, acc[g]);
 #pragma unroll
-        for (uint32_t qd = 0; qd < 4; ++qd) {
+        for (uint32_t qd = 0; qd < NQ; ++qd) {
           double sum[4];
 #pragma unroll
           for (uint32_t e = 0; e < 4; ++e) {
+            // Horner over the weight groups.  fma is used ONLY here, on integers below 2^53: t*256 + acc is exact, so the
+            // fused and the two-step form give the same bits (the reference-order arithmetic below stays unfused).
             double t = 0.0;
+            bool started = false;
 #pragma unroll
             for (int g = DENSE_MAX_GROUPS - 1; g >= 0; --g)
-              if ((uint32_t)g < ngr) t = __dadd_rn(__dmul_rn(t, 256.0), (double)acc[g][4 * qd + e]);
-            t = __dmul_rn(t, w0);
-            if (p.flags & 1u) t = __dadd_rn(t, part[(size_t)(c0 + 4 * qd + e) * 128]);
+              if ((uint32_t)g < ngr) {
+                t = started ? __fma_rn(t, 256.0, (double)acc[g][4 * qd + e]) : (double)acc[g][4 * qd + e];
+                started = true;
+              }
+            if (!NGR && w0 != 1.0) t = __dmul_rn(t, w0);
+            if (add_partial) t = __dadd_rn(t, part[(size_t)(c0 + 4 * qd + e) * 128]);
             sum[e] = t;
           }
+          const Cursor c = cw;
+          advance(cw);
           if (!final_round) {
 #pragma unroll
             for (uint32_t e = 0; e < 4; ++e) part[(size_t)(c0 + 4 * qd + e) * 128] = sum[e];
             continue;
           }
-          int32_t* gp = quad_ptr(c0 + 4 * qd);
+          int32_t* gp = quad_ptr(c);
           if (!gp) continue;
-          const unsigned long long qi = (unsigned long long)nt * 32u + ((c0 + 4 * qd) >> 2);
-          const uint32_t yl = (uint32_t)(qi / p.nxq), xq = (uint32_t)(qi - (unsigned long long)yl * p.nxq);
           const int4 o4 = own[qd];
           const double d[4] = {(double)(uint32_t)o4.x, (double)(uint32_t)o4.y, (double)(uint32_t)o4.z, (double)(uint32_t)o4.w};
           double x[4];
@@ -366,15 +395,23 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
           if (p.xout) {
 #pragma unroll
             for (uint32_t e = 0; e < 4; ++e) {
-              const uint32_t xc = xq * 4 + e;
-              if (xc < p.L.nx) p.xout[((size_t)yl * p.L.nx + xc) * p.L.nsp + sp] = x[e];
+              const uint32_t xc = c.xq * 4 + e;
+              if (xc < p.L.nx) p.xout[((size_t)c.yl * p.L.nx + xc) * p.L.nsp + sp] = x[e];
             }
             continue;
           }
-          const uint4 u = philox_rk(xq, p.L.y0 + yl, sp, (uint32_t)p.t0, p.rk);
+          const uint4 u = philox_rk(c.xq, p.L.y0 + c.yl, sp, (uint32_t)p.t0, p.rk);
+          // ROUND: in-range fast path decided per thread on the high words (negative x has the sign bit set -> huge)
+          const uint32_t hm = max(max((uint32_t)__double2hiint(x[0]), (uint32_t)__double2hiint(x[1])),
+                                  max((uint32_t)__double2hiint(x[2]), (uint32_t)__double2hiint(x[3])));
           int4 o;
-          o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
-          o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
+          if (hm >= 0x41DFFFFFu) {
+            o.x = round_stoch(x[0], u.x); o.y = round_stoch(x[1], u.y);
+            o.z = round_stoch(x[2], u.z); o.w = round_stoch(x[3], u.w);
+          } else {
+            o.x = round_stoch_inrange(x[0], u.x); o.y = round_stoch_inrange(x[1], u.y);
+            o.z = round_stoch_inrange(x[2], u.z); o.w = round_stoch_inrange(x[3], u.w);
+          }
           *reinterpret_cast<int4*>(gp) = o;
         }
       }

@@ -74,4 +74,13 @@ def test_sass_is_sm100a_with_bulk_copy(built):
     out = subprocess.run(["cuobjdump", "-sass", built], capture_output=True, text=True).stdout
     assert "sm_100a" in out
     assert "UBLKCP" in out          # cp.async.bulk (TMA unit) staging of the generate tiles
-    assert "DFMA" not in out        # no FP64 contraction anywhere: bit-exactness vs the reference's x86-64 build
+    # no FP64 contraction in the reference-order arithmetic: bit-exactness vs the reference's x86-64 build.  The one
+    # kernel allowed to hold DFMA is the tensor-core path, whose Horner recombination of integer accumulators is exact
+    # either way (k_dense.cuh); everything else must be free of it.
+    funcs = out.split("Function : ")
+    assert any("generate_dense_kernel" in f.split("\n", 1)[0] for f in funcs)
+    for f in funcs[1:]:
+        name = f.split("\n", 1)[0]
+        if "generate_dense_kernel" not in name:
+            assert "DFMA" not in f, name
+    assert "UTCIMMA" in out and "LDTM" in out     # tcgen05.mma kind::i8 and tcgen05.ld of the dense generate kernel
