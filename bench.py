@@ -444,6 +444,11 @@ def main():
     ap.add_argument("--dense-prof", action="store_true", dest="dense_prof")
     ap.add_argument("--dense-dmax", type=int, default=199, dest="dense_dmax")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: native libraries that write to file descriptor 1 (NCCL prints its version
+    # there) are diverted to stderr, Python's own stdout keeps the original descriptor
+    sys.stdout.flush()
+    sys.stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     if args.impl == "reference":
         run_reference(args)
