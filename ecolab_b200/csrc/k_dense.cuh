@@ -29,8 +29,8 @@
 //   warp 0 : producer   -- bulk copies of stage (tile, kc) into a ring, "full"/"empty" mbarriers
 //   warp 1 : MMA issuer -- one lane issues P*Q*(KC/32) tcgen05.mma per stage into <= 4 accumulators of 128 columns,
 //                          tcgen05.commit frees the stage / publishes the accumulators
-//   warps 2..9 : epilogue -- tcgen05.ld (lane = species row, 64 columns per warp), Horner, generate arithmetic,
-//                            Philox ROUND, STG.128; the densities of the next 16 columns are prefetched meanwhile
+//   warps 2..17 : epilogue -- tcgen05.ld (lane = species row, 32 columns per warp), Horner, generate arithmetic,
+//                            Philox ROUND, STG.128; the densities of the next 8 columns are prefetched meanwhile
 #pragma once
 #include "k_common.cuh"
 #include "k_generate.cuh"
@@ -300,7 +300,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
       if (p.prof) { p.prof[blockIdx.x * 8 + 0] = pc[0]; p.prof[blockIdx.x * 8 + 1] = pc[1]; p.prof[blockIdx.x * 8 + 2] = pc[2]; p.prof[blockIdx.x * 8 + 3] = k; }
     }
   } else {
-    // ===================== epilogue (warps 2..9; TMEM lanes 32*(warp%4).., columns 64*((warp-2)/4)..) =====================
+    // ===================== epilogue (warps 2..17; TMEM lanes 32*(warp%4).., columns DENSE_EPI_COLS*((warp-2)/4)..) =====================
     const uint32_t lq = warp & 3u, row = lq * 32u + lane, cbase = ((warp - 2u) >> 2) * DENSE_EPI_COLS;
     const uint32_t ngr = NGR ? (uint32_t)NGR : p.g1 - p.g0;
     const uint32_t qsh = p.L.tw == 4 ? 0u : p.L.tw == 8 ? 1u : p.L.tw == 16 ? 2u : 3u;   // log2(quads per density tile)
