@@ -100,3 +100,36 @@ def test_dense_auto_selection_and_sparse_agreement(oracle_mod, gpu):
     sp = load_gpu(gpu, synth(nsp, 3, 5), d, grid, seed=2)
     sp.generate(1)
     assert sp._scalar("dense_active") == 0
+
+
+def test_dense_condense_and_multi_step(oracle_mod, gpu):
+    """generate(niter) in one call, then condense (species rows removed -> beta re-sliced for the new species count),
+    then generate again: still bit-exact on the dyadic model."""
+    grid, nsp = (20, 3), 140
+    p = dyadic(nsp, 8, 200)
+    d = densities(grid[0] * grid[1], nsp, 8, dmax=200)
+    d[:, [3, 77, 139]] = 0                      # extinct everywhere -> condense removes them
+    o = load_oracle(oracle_mod, p, d, grid, seed=4)
+    m = load_gpu(gpu, p, d, grid, seed=4)
+    m.set_tuning("gen_dense", 1)
+    o.generate(3); m.generate(3)
+    assert np.array_equal(m.density_array(), o.get_density_all())
+    assert m.condense() == o.condense() >= 3
+    o.generate(2); m.generate(2)
+    assert m._scalar("dense_active") == 1
+    assert np.array_equal(m.density_array(), o.get_density_all())
+
+
+def test_dense_step_host_bands(oracle_mod, gpu):
+    """eco_step_host runs generate band by band (row offsets enter the Philox counters and the operand packing)."""
+    grid, nsp = (33, 40), 130
+    p = dyadic(nsp, 12, 150)
+    d = densities(grid[0] * grid[1], nsp, 12, dmax=150)
+    o = load_oracle(oracle_mod, p, d, grid, seed=6)
+    m = load_gpu(gpu, p, d, grid, seed=6)
+    m.set_tuning("gen_dense", 1)
+    out = np.empty_like(d)
+    o.generate(1)
+    moved = o.migrate()
+    assert m.step_host(d, out, 1) == moved
+    assert np.array_equal(out, o.get_density_all())
