@@ -197,7 +197,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
 // generate(niter > 1): per tile, `niter` Jacobi steps between two shared-memory buffers (HBM traffic amortised
 // over niter -- the scripts' cadence is generate(100), models/spatial_ecolab.py:67), CTA-wide barrier per step.
 // ---------------------------------------------------------------------------------------------------------
-template <int TW, int THREADS>
+template <int TW, int THREADS, bool BSMEM>
 __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -207,10 +207,14 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
   int32_t* buf1 = buf0 + tile_words;
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + (size_t)tile_bytes * 2);
   uint32_t* s_boff = reinterpret_cast<uint32_t*>(bar + 1);
+  uint4* s_stream = reinterpret_cast<uint4*>(smem_raw + (((size_t)tile_bytes * 2 + 8 + 4 * (nblocks + 1)) + 15) / 16 * 16);
 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = THREADS / 32;
   const uint32_t rr = LaneMap<TW>::row(lane), q = LaneMap<TW>::quad(lane);
   for (uint32_t i = threadIdx.x; i <= nblocks; i += THREADS) s_boff[i] = p.boff[i];
+  if (BSMEM)
+    for (uint32_t i = threadIdx.x; i < p.stream_recs; i += THREADS) s_stream[i] = __ldg(p.stream + i);
+  const uint4* strm = BSMEM ? s_stream : p.stream;
   if (threadIdx.x == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -241,7 +245,7 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
         if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
           const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
           double x[4];
-          gen_x<TW, false>(lp, own, p.stream + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+          gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
           o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
         }
         *reinterpret_cast<int4*>(dst + row * TW + 4 * q) = o;

@@ -12,37 +12,61 @@ __device__ __forceinline__ size_t cell_addr(const Layout& L, uint32_t yl, uint32
 // ---------------------------------------------------------------------------------------------
 // condense (reference SpatialModel::condense :171-196, EcolabPoint::condense :124-137)
 // ---------------------------------------------------------------------------------------------
-// mask[s] = 1 iff some owned cell has n != 0 (benign race: all writers store 1, as in the reference :176)
+// mask[s] = 1 iff some owned cell has n != 0 (benign race: all writers store 1, as in the reference :176).
+// A CTA first records what it sees in a shared-memory copy of the mask and only stores a flag that is not yet set there:
+// once every living species has been seen (after the first tile or two) the pass is pure 16-byte loads.
 __global__ void __launch_bounds__(256) alive_kernel(const Layout L, uint8_t* mask) {
-  const uint32_t ntiles = L.ntx * L.ny, per = L.nsp * L.tw / 4;
+  extern __shared__ uint8_t s_alive[];                 // [nsp]
+  for (uint32_t i = threadIdx.x; i < L.nsp; i += blockDim.x) s_alive[i] = 0;
+  __syncthreads();
+  const uint32_t ntiles = L.ntx * L.ny, qpr = L.tw / 4, per = L.nsp * qpr;
   for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int4* t = reinterpret_cast<const int4*>(L.base + (size_t)tile * L.tile_stride);
+#pragma unroll 4
     for (uint32_t i = threadIdx.x; i < per; i += blockDim.x) {
-      const int4 v = t[i];
-      if (v.x | v.y | v.z | v.w) mask[i / (L.tw / 4)] = 1;
+      const int4 v = __ldcs(t + i);
+      if (v.x | v.y | v.z | v.w) {
+        const uint32_t sp = i / qpr;
+        if (!s_alive[sp]) s_alive[sp] = 1;
+      }
     }
   }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < L.nsp; i += blockDim.x)
+    if (s_alive[i]) mask[i] = 1;
 }
 
 // in-place, order-preserving row compaction inside each tile (ghost rows included); map[s] = new index of kept row s.
-// Rows are moved in chunks: every row of a chunk is in registers before any is overwritten, and map[s] <= s.
-__global__ void __launch_bounds__(1024) compact_kernel(int32_t* buf, size_t tile_stride, uint32_t tw, uint32_t ntiles,
-                                                       uint32_t nsp_old, uint32_t nkeep, const uint8_t* keep,
-                                                       const uint32_t* map) {
-  const uint32_t cx = threadIdx.x % tw, r = threadIdx.x / tw, ch = blockDim.x / tw;
-  for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    int32_t* t = buf + (size_t)tile * tile_stride;
-    for (uint32_t c0 = 0; c0 < nsp_old; c0 += ch) {
-      const uint32_t s = c0 + r;
-      int v = 0;
-      bool k = false;
-      if (s < nsp_old) { v = t[(size_t)s * tw + cx]; k = keep[s] != 0; }
-      __syncthreads();
-      if (k) t[(size_t)map[s] * tw + cx] = v;
-      __syncthreads();
+// One warp per tile, 512 contiguous bytes (128/tw species rows) per step: all rows of a step are in registers before any
+// is stored, and map[s] <= s, so a store never lands on a row that has not been read yet.  No block barriers.
+__global__ void __launch_bounds__(256) compact_kernel(int32_t* buf, size_t tile_stride, uint32_t tw, uint32_t ntiles,
+                                                      uint32_t nsp_old, uint32_t nkeep, const uint8_t* __restrict__ keep,
+                                                      const uint32_t* __restrict__ map) {
+  const uint32_t lane = threadIdx.x & 31u, wpb = blockDim.x >> 5;
+  const uint32_t qpr = tw / 4, rows = 32 / qpr;         // lanes per species row, species rows per warp step
+  const uint32_t rr = lane / qpr, q = lane % qpr;
+  constexpr int U = 4;                                  // steps in flight
+  for (uint32_t tile = blockIdx.x * wpb + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.x * wpb) {
+    int32_t* t = buf + (size_t)tile * tile_stride + 4 * q;
+    for (uint32_t s0 = 0; s0 < nsp_old; s0 += rows * U) {
+      int4 v[U];
+      uint32_t dst[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t sp = s0 + u * rows + rr;
+        dst[u] = 0xffffffffu;
+        if (sp < nsp_old) {
+          v[u] = *reinterpret_cast<const int4*>(t + (size_t)sp * tw);
+          if (__ldg(keep + sp)) dst[u] = __ldg(map + sp);
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (dst[u] != 0xffffffffu) *reinterpret_cast<int4*>(t + (size_t)dst[u] * tw) = v[u];
+      __syncwarp();
     }
-    for (uint32_t s = nkeep + r; s < nsp_old; s += ch) t[(size_t)s * tw + cx] = 0;
-    __syncthreads();
+    for (uint32_t sp = nkeep + rr; sp < nsp_old; sp += rows) *reinterpret_cast<int4*>(t + (size_t)sp * tw) = make_int4(0, 0, 0, 0);
   }
 }
 
@@ -117,17 +141,22 @@ __global__ void birth_kernel(const Layout L, uint32_t s0, const uint32_t* cells,
 // ---------------------------------------------------------------------------------------------
 // observables
 // ---------------------------------------------------------------------------------------------
-// living species per owned cell (EcolabPoint::nsp, models/ecolab_model.cc:114-122); one CTA per tile
+// living species per owned cell (EcolabPoint::nsp, models/ecolab_model.cc:114-122); one CTA per tile, 16-byte loads
 __global__ void __launch_bounds__(256) nsp_cell_kernel(const Layout L, uint32_t* out) {
   __shared__ uint32_t cnt[32];
-  const uint32_t ntiles = L.ntx * L.ny, per = L.nsp * L.tw;
+  const uint32_t ntiles = L.ntx * L.ny, qpr = L.tw / 4, per = L.nsp * qpr;
   for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     if (threadIdx.x < 32) cnt[threadIdx.x] = 0;
     __syncthreads();
-    const int32_t* t = L.base + (size_t)tile * L.tile_stride;
-    uint32_t c = 0;                      // blockDim is a multiple of tw: a thread always sees the same cell column
-    for (uint32_t i = threadIdx.x; i < per; i += blockDim.x) c += t[i] != 0;
-    atomicAdd(&cnt[threadIdx.x % L.tw], c);
+    const int4* t = reinterpret_cast<const int4*>(L.base + (size_t)tile * L.tile_stride);
+    uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;   // blockDim is a multiple of qpr: a thread always sees the same 4 cell columns
+#pragma unroll 4
+    for (uint32_t i = threadIdx.x; i < per; i += blockDim.x) {
+      const int4 v = __ldcs(t + i);
+      c0 += v.x != 0; c1 += v.y != 0; c2 += v.z != 0; c3 += v.w != 0;
+    }
+    const uint32_t q = threadIdx.x % qpr;
+    atomicAdd(&cnt[4 * q], c0); atomicAdd(&cnt[4 * q + 1], c1); atomicAdd(&cnt[4 * q + 2], c2); atomicAdd(&cnt[4 * q + 3], c3);
     __syncthreads();
     const uint32_t yl = tile / L.ntx, tx = tile - yl * L.ntx, x = tx * L.tw + threadIdx.x;
     if (threadIdx.x < L.tw && x < L.nx) out[(size_t)yl * L.nx + x] = cnt[threadIdx.x];
