@@ -174,7 +174,7 @@ def build_model(E, args, nx, ny, comm, device, stream):
     m.setGrid(nx, ny)
     m.seed(10)
     for knob, val in (("gen_threads", args.gen_warps), ("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem),
-                      ("mig_variant", args.mig_variant)):
+                      ("mig_variant", args.mig_variant), ("gen_dual", args.gen_dual)):
         if val:
             m.set_tuning(knob, val)
     m.fill_density_random(0, 199)   # mean 100, with gradients between neighbours so migrate really moves population
@@ -436,6 +436,7 @@ def main():
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
     ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
     ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")
+    ap.add_argument("--gen-dual", type=int, default=0, dest="gen_dual")
     ap.add_argument("--e2e-unpipelined", action="store_true", dest="e2e_unpipelined")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -121,6 +121,7 @@ class Engine {
   int gen_variant = 0;
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory
+  int gen_dual = 0;      // generate(1): two species-row blocks per consumer warp at a time; 0 = auto, 1 = on, -1 = off
   int mig_variant = 0;
   // dense (tensor-core) generate, k_dense.cuh.  gen_dense: 0 = automatic (beta at least half full and >= 128 species),
   // 1 = always, -1 = never.  dense_slices = P, the 8-bit slices beta is cut into (3: 2^-24 of the row maximum; 7: FP64).
@@ -163,6 +164,7 @@ class Engine {
   uint32_t nblocks_ = 0, beta_tw_ = 0, beta_nsp_ = 0;   // ELL blocks; the tile width / species count it was built for
   uint32_t* d_boff_ = nullptr; void* d_stream_ = nullptr;   // blocked-ELL stream (k_generate.cuh)
   size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_slots_ = 0;
+  uint32_t beta_uslots_ = 0;   // != 0: every block of the stream has this many slots (uniform width, no offset table reads)
   BetaCsr beta_host_;                                   // kept to re-block when the tile width changes
 
   // dense path operands (k_dense.cuh)

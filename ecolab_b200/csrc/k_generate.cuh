@@ -25,18 +25,40 @@ struct GenParams {
   unsigned long long t0;
   uint32_t nstages;          // pipeline kernel: shared-memory tile buffers
   uint32_t stream_recs;      // records in `stream` (BSMEM kernels copy it into shared memory)
+  uint32_t uslots;           // != 0: every block has exactly `uslots` slots (header + uslots-1 terms), boff[b] = b*uslots
   uint32_t rk[20];           // Philox round keys {k0_r, k1_r}, r = 0..9, for (seed, t0 >> 32): host-computed
 };
 
-template <bool BSMEM>
-__device__ __forceinline__ uint4 ldrec(const uint4* p) {
-  if (BSMEM) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
-    return v;
-  }
-  return __ldg(p);
+__device__ __forceinline__ uint4 lds128u(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
 }
+__device__ __forceinline__ int4 lds128i(uint32_t a) {
+  int4 v;
+  asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+
+// This lane's column of beta records of one block: the shared-memory copy (32-bit shared address, BSMEM) or the
+// stream in global memory (through L1).  Record j of the lane lives j*ROWS records further on.
+template <int TW, bool BSMEM>
+struct RecCol {
+  uint32_t a;
+  const uint4* p;
+  __device__ __forceinline__ uint4 ld(int j) const {
+    constexpr int R = LaneMap<TW>::ROWS;
+    if (BSMEM) return lds128u(a + (uint32_t)j * R * 16u);
+    return __ldg(p + j * R);
+  }
+  __device__ __forceinline__ RecCol advance(int j) const {
+    constexpr int R = LaneMap<TW>::ROWS;
+    RecCol r;
+    r.a = a + (uint32_t)j * R * 16u;
+    r.p = p + j * R;
+    return r;
+  }
+};
 
 // Philox4x32-10 with the key schedule taken from kernel parameters (constant bank operands, no key arithmetic)
 __device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t (&rk)[20]) {
@@ -53,35 +75,78 @@ __device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2
 
 __device__ __forceinline__ double dbl(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
 
-// One warp-op: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of species row `row`.
-// `lp` = shared-memory tile + 4*quad (ints); `own` = the lane's own densities; `blk` = this lane's header record of
-// block b (global memory, or the shared-memory copy when BSMEM); W = terms per row.
-template <int TW, bool BSMEM>
-__device__ __forceinline__ void gen_x(const int32_t* __restrict__ lp, const int4 own, const uint4* __restrict__ blk,
-                                      uint32_t W, double x[4]) {
-  constexpr int R = LaneMap<TW>::ROWS;
-  const uint4 h = ldrec<BSMEM>(blk);
-  const double diag = dbl(h.x, h.y), rr = dbl(h.z, h.w);
-  const double d0 = (double)(uint32_t)own.x, d1 = (double)(uint32_t)own.y, d2 = (double)(uint32_t)own.z,
-               d3 = (double)(uint32_t)own.w;
-  double ir0 = __dmul_rn(diag, d0), ir1 = __dmul_rn(diag, d1), ir2 = __dmul_rn(diag, d2), ir3 = __dmul_rn(diag, d3);
-  const uint4* e = blk + R;
-#pragma unroll 4
-  for (uint32_t j = 0; j < W; ++j, e += R) {
-    const uint4 w = ldrec<BSMEM>(e);
-    const double v = dbl(w.x, w.y);
-    const int4 g = *reinterpret_cast<const int4*>(reinterpret_cast<const char*>(lp) + w.z);
-    // int -> double on the conversion (XU) pipe, which is otherwise idle; multiply and accumulate stay two
-    // individually rounded FP64 operations (no contraction: -fmad=false)
-    ir0 = __dadd_rn(ir0, __dmul_rn(v, (double)(uint32_t)g.x));
-    ir1 = __dadd_rn(ir1, __dmul_rn(v, (double)(uint32_t)g.y));
-    ir2 = __dadd_rn(ir2, __dmul_rn(v, (double)(uint32_t)g.z));
-    ir3 = __dadd_rn(ir3, __dmul_rn(v, (double)(uint32_t)g.w));
+// ir += val_j * n[col_j] for NT consecutive terms starting at record column `e`, in term order, for NS independent
+// warp-ops (species-row blocks) of the same tile at once.  All records are loaded first, then all gathers, then the
+// arithmetic: the loads of one term never wait for the previous term, and with NS = 2 every dependent chain has an
+// independent twin to hide its latency.  int -> double runs on the conversion (XU) pipe, which is otherwise idle;
+// multiply and accumulate stay two individually rounded FP64 operations (no contraction: -fmad=false).
+template <int TW, bool BSMEM, int NS, int NT>
+__device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (&e)[NS], double (&ir)[NS][4]) {
+  uint4 w[NS][NT];
+  int4 g[NS][NT];
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int j = 0; j < NT; ++j) w[s][j] = e[s].ld(j);
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int j = 0; j < NT; ++j) g[s][j] = lds128i(lp + w[s][j].z);
+#pragma unroll
+  for (int j = 0; j < NT; ++j)
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      const double v = dbl(w[s][j].x, w[s][j].y);
+      ir[s][0] = __dadd_rn(ir[s][0], __dmul_rn(v, (double)(uint32_t)g[s][j].x));
+      ir[s][1] = __dadd_rn(ir[s][1], __dmul_rn(v, (double)(uint32_t)g[s][j].y));
+      ir[s][2] = __dadd_rn(ir[s][2], __dmul_rn(v, (double)(uint32_t)g[s][j].z));
+      ir[s][3] = __dadd_rn(ir[s][3], __dmul_rn(v, (double)(uint32_t)g[s][j].w));
+    }
+}
+
+// NS warp-ops: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of one species row each.
+// `lp` = shared address of the tile + 16*quad; `own` = the lane's own densities; `blk` = this lane's record column
+// of the block (header first); W = terms per row (warp-uniform, the same for all NS blocks).
+template <int TW, bool BSMEM, int NS>
+__device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], const RecCol<TW, BSMEM> (&blk)[NS], uint32_t W,
+                                        double (&x)[NS][4]) {
+  double d[NS][4], ir[NS][4], rr[NS];
+  RecCol<TW, BSMEM> e[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) {
+    const uint4 h = blk[s].ld(0);
+    const double diag = dbl(h.x, h.y);
+    rr[s] = dbl(h.z, h.w);
+    d[s][0] = (double)(uint32_t)own[s].x; d[s][1] = (double)(uint32_t)own[s].y;
+    d[s][2] = (double)(uint32_t)own[s].z; d[s][3] = (double)(uint32_t)own[s].w;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ir[s][k] = __dmul_rn(diag, d[s][k]);
+    e[s] = blk[s].advance(1);
   }
-  x[0] = __dadd_rn(d0, __dmul_rn(d0, __dadd_rn(rr, ir0)));
-  x[1] = __dadd_rn(d1, __dmul_rn(d1, __dadd_rn(rr, ir1)));
-  x[2] = __dadd_rn(d2, __dmul_rn(d2, __dadd_rn(rr, ir2)));
-  x[3] = __dadd_rn(d3, __dmul_rn(d3, __dadd_rn(rr, ir3)));
+  for (; W >= 4; W -= 4) {
+    gen_terms<TW, BSMEM, NS, 4>(lp, e, ir);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) e[s] = e[s].advance(4);
+  }
+  switch (W) {   // warp-uniform
+    case 3: gen_terms<TW, BSMEM, NS, 3>(lp, e, ir); break;
+    case 2: gen_terms<TW, BSMEM, NS, 2>(lp, e, ir); break;
+    case 1: gen_terms<TW, BSMEM, NS, 1>(lp, e, ir); break;
+    default: break;
+  }
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) x[s][k] = __dadd_rn(d[s][k], __dmul_rn(d[s][k], __dadd_rn(rr[s], ir[s][k])));
+}
+
+template <int TW, bool BSMEM>
+__device__ __forceinline__ void gen_x(uint32_t lp, const int4 own, const RecCol<TW, BSMEM>& blk, uint32_t W, double x[4]) {
+  const int4 o1[1] = {own};
+  const RecCol<TW, BSMEM> b1[1] = {blk};
+  double x1[1][4];
+  gen_x_n<TW, BSMEM, 1>(lp, o1, b1, W, x1);
+  x[0] = x1[0][0]; x[1] = x1[0][1]; x[2] = x1[0][2]; x[3] = x1[0][3];
 }
 
 // ROUND of the lane's four values.  Fast path: 0 <= x < 2^31-256 for all four (decided on the high words with
@@ -99,6 +164,24 @@ __device__ __forceinline__ int4 round4(const double x[4], const uint4 u) {
     o.z = round_stoch_inrange(x[2], u.z); o.w = round_stoch_inrange(x[3], u.w);
   }
   return o;
+}
+
+// the same for two warp-ops with ONE range decision (one vote, one branch)
+__device__ __forceinline__ void round4x2(const double (&x)[2][4], const uint4 u0, const uint4 u1, int4& o0, int4& o1) {
+  uint32_t hm = 0;
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) hm = max(hm, (uint32_t)__double2hiint(x[s][k]));
+  if (__any_sync(FULL, hm >= 0x41DFFFFFu)) {
+    o0.x = round_stoch(x[0][0], u0.x); o0.y = round_stoch(x[0][1], u0.y); o0.z = round_stoch(x[0][2], u0.z); o0.w = round_stoch(x[0][3], u0.w);
+    o1.x = round_stoch(x[1][0], u1.x); o1.y = round_stoch(x[1][1], u1.y); o1.z = round_stoch(x[1][2], u1.z); o1.w = round_stoch(x[1][3], u1.w);
+  } else {
+    o0.x = round_stoch_inrange(x[0][0], u0.x); o0.y = round_stoch_inrange(x[0][1], u0.y);
+    o0.z = round_stoch_inrange(x[0][2], u0.z); o0.w = round_stoch_inrange(x[0][3], u0.w);
+    o1.x = round_stoch_inrange(x[1][0], u1.x); o1.y = round_stoch_inrange(x[1][1], u1.y);
+    o1.z = round_stoch_inrange(x[1][2], u1.z); o1.w = round_stoch_inrange(x[1][3], u1.w);
+  }
 }
 
 __device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t* src, uint32_t tile_bytes, uint64_t* bar) {
@@ -120,7 +203,9 @@ __device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t*
 //                    no CTA-wide barrier exists: a warp that is done with a tile moves on to the next one.
 // Results go straight from registers to HBM as 16-byte vectors (a warp-op writes 512 contiguous bytes), in place.
 // ---------------------------------------------------------------------------------------------------------
-template <int TW, int NW, bool BSMEM>
+// NS = 2 (uniform-width beta stream only, p.uslots != 0): a consumer warp takes two adjacent blocks of species rows at a
+// time and runs them as one instruction stream -- twice the independent work per warp for the same number of warps.
+template <int TW, int NW, bool BSMEM, int NS = 1>
 __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -136,7 +221,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
   for (uint32_t i = threadIdx.x; i <= nblocks; i += (NW + 1) * 32) s_boff[i] = p.boff[i];
   if (BSMEM)
     for (uint32_t i = threadIdx.x; i < p.stream_recs; i += (NW + 1) * 32) s_stream[i] = __ldg(p.stream + i);
-  const uint4* strm = BSMEM ? s_stream : p.stream;
   if (threadIdx.x == 0) {
     for (uint32_t s = 0; s < S; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, NW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -158,31 +242,83 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
 
   const uint32_t rr = LaneMap<TW>::row(lane), q = LaneMap<TW>::quad(lane);
   const uint32_t nbm = nblocks % NW;
+  const uint32_t tiles_s = smem_u32(tiles) + 16u * q, strm_s = smem_u32(s_stream) + 16u * rr, boff_s = smem_u32(s_boff);
+  const uint32_t uslots = p.uslots;
+  if constexpr (NS == 2) {
+    const uint32_t npairs = (nblocks + 1) / 2, npm = npairs % NW;
+    const uint32_t W = uslots - 1u, blk_bytes = uslots * (R * 16u);
+    uint32_t first = warp, stage = 0, round = 0;
+    for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
+      mbar_wait(full + stage, round & 1u);
+      const uint32_t lp = tiles_s + stage * tile_bytes;
+      int32_t* gl = p.L.base + (size_t)tile_id * p.L.tile_stride + 4 * q + rr * TW;
+      asm volatile("" : "+l"(gl));
+      const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
+      const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
+      for (uint32_t pr = first; pr < npairs; pr += NW) {
+        const uint32_t b0 = 2 * pr;
+        const bool has1 = b0 + 1 < nblocks;            // warp-uniform; false only for the last pair of an odd block count
+        const uint32_t b1 = has1 ? b0 + 1 : b0;
+        const uint32_t a0 = lp + b0 * (R * TW * 4u) + rr * (TW * 4u);
+        int4 own[2];
+        own[0] = lds128i(a0);
+        own[1] = lds128i(a0 + (b1 - b0) * (R * TW * 4u));
+        if (!__any_sync(FULL, (own[0].x | own[0].y | own[0].z | own[0].w | own[1].x | own[1].y | own[1].z | own[1].w) != 0)) continue;
+        RecCol<TW, BSMEM> blk[2];
+        blk[0].a = strm_s + b0 * blk_bytes; blk[0].p = p.stream + (size_t)b0 * uslots * R + rr;
+        blk[1].a = strm_s + b1 * blk_bytes; blk[1].p = p.stream + (size_t)b1 * uslots * R + rr;
+        double x[2][4];
+        gen_x_n<TW, BSMEM, 2>(lp, own, blk, W, x);
+        const uint32_t row0 = b0 * R + rr, row1 = b1 * R + rr;
+        const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row1, (uint32_t)p.t0, p.rk);
+        int4 o0, o1;
+        round4x2(x, u0, u1, o0, o1);
+        __stcs(reinterpret_cast<int4*>(gl + b0 * (R * TW)), o0);
+        if (has1) __stcs(reinterpret_cast<int4*>(gl + b1 * (R * TW)), o1);
+      }
+      first += NW - npm;
+      if (first >= NW) first -= NW;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + stage);
+      if (++stage == S) { stage = 0; ++round; }
+    }
+    return;
+  }
   uint32_t first = warp, stage = 0, round = 0;
   for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
     mbar_wait(full + stage, round & 1u);
-    const int32_t* lp = tiles + (size_t)stage * tile_words + 4 * q;
-    int32_t* gl = p.L.base + (size_t)tile_id * p.L.tile_stride + 4 * q;
+    const uint32_t lp = tiles_s + stage * tile_bytes;
+    int32_t* gl = p.L.base + (size_t)tile_id * p.L.tile_stride + 4 * q + rr * TW;
+    asm volatile("" : "+l"(gl));   // keep the tile's output pointer in registers (no per-warp-op 64-bit multiply)
     const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
     const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
     for (uint32_t b = first; b < nblocks; b += NW) {
       const uint32_t row = b * R + rr;
-      const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
+      const int4 own = lds128i(lp + b * (R * TW * 4u) + rr * (TW * 4u));
       // n = 0 stays 0 (x = 0 + 0*(...) = 0, ROUND(0) = 0): a warp-op whose 128 densities are all extinct is skipped
       if (!__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) continue;
-      const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
+      uint32_t s0, W;
+      if (uslots) { s0 = b * uslots; W = uslots - 1u; }
+      else {
+        uint32_t s1;
+        asm volatile("ld.shared.u32 %0, [%2];\n\tld.shared.u32 %1, [%2+4];" : "=r"(s0), "=r"(s1) : "r"(boff_s + 4u * b));
+        W = s1 - s0 - 1u;
+      }
+      RecCol<TW, BSMEM> blk;
+      blk.a = strm_s + s0 * (R * 16u);
+      blk.p = p.stream + (size_t)s0 * R + rr;
       double x[4];
 #ifndef ECO_ABLATE
-      gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+      gen_x<TW, BSMEM>(lp, own, blk, W, x);
       const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
-      __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
+      __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
 #else   // cost-attribution builds (tools/ablate.sh): results are wrong on purpose, never shipped
-      gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, (ECO_ABLATE & 2) ? 0u : s1 - s0 - 1u, x);
+      gen_x<TW, BSMEM>(lp, own, blk, (ECO_ABLATE & 2) ? 0u : W, x);
       const uint4 u = (ECO_ABLATE & 1) ? make_uint4(row, row * 3u, xq, yg) : philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk);
       int4 o;
       if (ECO_ABLATE & 4) o = make_int4(__double2loint(x[0]) ^ u.x, __double2loint(x[1]) ^ u.y, __double2loint(x[2]) ^ u.z, __double2loint(x[3]) ^ u.w);
       else o = round4(x, u);
-      if (!(ECO_ABLATE & 8) || o.x == 0x7fffffff) __stcs(reinterpret_cast<int4*>(gl + row * TW), o);
+      if (!(ECO_ABLATE & 8) || o.x == 0x7fffffff) __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
 #endif
     }
     first += NW - nbm;
@@ -223,6 +359,7 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
 
   const uint32_t ntiles = p.L.ntx * p.L.ny;
   uint32_t phase = 0;
+  const uint32_t buf0_s = smem_u32(buf0) + 16u * q, strm_s = smem_u32(s_stream) + 16u * rr;
   for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
     int32_t* gt = p.L.base + (size_t)tile_id * p.L.tile_stride;
     if (threadIdx.x == 0) {
@@ -236,22 +373,26 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
     const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
     int32_t* src = buf0;
     int32_t* dst = buf1;
+    uint32_t lp = buf0_s, lq = buf0_s + tile_bytes;   // shared addresses of src / dst (+ 16*quad)
     for (uint32_t step = 0; step < p.niter; ++step) {
-      const int32_t* lp = src + 4 * q;
       for (uint32_t b = warp; b < nblocks; b += nwarps) {
         const uint32_t row = b * R + rr;
-        const int4 own = *reinterpret_cast<const int4*>(lp + row * TW);
+        const int4 own = lds128i(lp + row * (TW * 4u));
         int4 o = make_int4(0, 0, 0, 0);
         if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
           const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
+          RecCol<TW, BSMEM> blk;
+          blk.a = strm_s + s0 * (R * 16u);
+          blk.p = strm + (size_t)s0 * R + rr;
           double x[4];
-          gen_x<TW, BSMEM>(lp, own, strm + (size_t)s0 * R + rr, s1 - s0 - 1u, x);
+          gen_x<TW, BSMEM>(lp, own, blk, s1 - s0 - 1u, x);
           o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
         }
-        *reinterpret_cast<int4*>(dst + row * TW + 4 * q) = o;
+        asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
       }
       __syncthreads();
       int32_t* tmp = src; src = dst; dst = tmp;
+      const uint32_t tl = lp; lp = lq; lq = tl;
     }
     const int4* s4 = reinterpret_cast<const int4*>(src);
     int4* g4 = reinterpret_cast<int4*>(gt);

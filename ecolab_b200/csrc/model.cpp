@@ -975,6 +975,7 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   else if (k == "mig_variant") m->eng.mig_variant = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
   else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;
+  else if (k == "gen_dual") m->eng.gen_dual = value;
   else if (k == "gen_dense") m->eng.gen_dense = value;
   else if (k == "dense_slices") {
     if (value < 1 || value > 7) throw std::runtime_error("dense_slices must be 1..7");

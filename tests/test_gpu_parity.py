@@ -39,6 +39,20 @@ def test_generate_bit_exact(oracle_mod, gpu, grid, nsp, k):
         assert m.tstep() == int(o.get("tstep"))
 
 
+@pytest.mark.parametrize("grid,nsp,k", [((8, 5), 37, 3), ((33, 3), 64, 5), ((70, 9), 129, 3), ((17, 4), 1000, 3), ((5, 3), 8, 1),
+                                        ((9, 2), 200, 0)])
+@pytest.mark.parametrize("warps", [0, 12])
+def test_generate_dual_block_consumers(oracle_mod, gpu, grid, nsp, k, warps):
+    """generate(1) with two species-row blocks per consumer warp (knob gen_dual): same bits, odd block counts included."""
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k)
+    m.set_tuning("gen_dual", 1)
+    if warps:
+        m.set_tuning("gen_threads", warps)
+    for _ in range(3):
+        o.generate(1); m.generate(1)
+        assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+
+
 @pytest.mark.parametrize("grid,nsp,k", [(None, 100, 3), ((8, 5), 37, 3), ((33, 3), 64, 16)])
 def test_pre_rounding_float_update(oracle_mod, gpu, grid, nsp, k):
     o, m, grid = pair(oracle_mod, gpu, grid, nsp, k)
