@@ -75,6 +75,22 @@ __device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2
 
 __device__ __forceinline__ double dbl(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
 
+// int -> double of a density.  Two exact routes: I2F on the conversion (XU) pipe -- one issue slot, 8 pipe cycles per
+// warp on a quarter-rate unit -- or (2^52+n) - 2^52 on the FP64 pipe -- three issue slots (pair build + DADD), 2 pipe
+// cycles.  ECO_GEN_CVT_G: gathered densities of term j go through FP64 when bit (j & 1) of the mask is set (0 = all XU,
+// 3 = all FP64, 2 = odd terms only); ECO_GEN_CVT_OWN likewise for the lane's own densities.
+#ifndef ECO_GEN_CVT_G
+#define ECO_GEN_CVT_G 2      // measured on C3, 3 terms: 0 -> 2.20 ms, 2 -> 2.14, 3 -> 2.15; own densities through FP64: no gain
+#endif
+#ifndef ECO_GEN_CVT_OWN
+#define ECO_GEN_CVT_OWN 0
+#endif
+template <bool FP64PIPE>
+__device__ __forceinline__ double cvt_n(int n) {
+  if (FP64PIPE) return u2d((uint32_t)n);
+  return (double)(uint32_t)n;
+}
+
 // ir += val_j * n[col_j] for NT consecutive terms starting at record column `e`, in term order, for NS independent
 // warp-ops (species-row blocks) of the same tile at once.  All records are loaded first, then all gathers, then the
 // arithmetic: the loads of one term never wait for the previous term, and with NS = 2 every dependent chain has an
@@ -97,10 +113,17 @@ __device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
       const double v = dbl(w[s][j].x, w[s][j].y);
-      ir[s][0] = __dadd_rn(ir[s][0], __dmul_rn(v, (double)(uint32_t)g[s][j].x));
-      ir[s][1] = __dadd_rn(ir[s][1], __dmul_rn(v, (double)(uint32_t)g[s][j].y));
-      ir[s][2] = __dadd_rn(ir[s][2], __dmul_rn(v, (double)(uint32_t)g[s][j].z));
-      ir[s][3] = __dadd_rn(ir[s][3], __dmul_rn(v, (double)(uint32_t)g[s][j].w));
+      if ((ECO_GEN_CVT_G >> (j & 1)) & 1) {
+        ir[s][0] = __dadd_rn(ir[s][0], __dmul_rn(v, cvt_n<true>(g[s][j].x)));
+        ir[s][1] = __dadd_rn(ir[s][1], __dmul_rn(v, cvt_n<true>(g[s][j].y)));
+        ir[s][2] = __dadd_rn(ir[s][2], __dmul_rn(v, cvt_n<true>(g[s][j].z)));
+        ir[s][3] = __dadd_rn(ir[s][3], __dmul_rn(v, cvt_n<true>(g[s][j].w)));
+      } else {
+        ir[s][0] = __dadd_rn(ir[s][0], __dmul_rn(v, cvt_n<false>(g[s][j].x)));
+        ir[s][1] = __dadd_rn(ir[s][1], __dmul_rn(v, cvt_n<false>(g[s][j].y)));
+        ir[s][2] = __dadd_rn(ir[s][2], __dmul_rn(v, cvt_n<false>(g[s][j].z)));
+        ir[s][3] = __dadd_rn(ir[s][3], __dmul_rn(v, cvt_n<false>(g[s][j].w)));
+      }
     }
 }
 
@@ -117,8 +140,8 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     const uint4 h = blk[s].ld(0);
     const double diag = dbl(h.x, h.y);
     rr[s] = dbl(h.z, h.w);
-    d[s][0] = (double)(uint32_t)own[s].x; d[s][1] = (double)(uint32_t)own[s].y;
-    d[s][2] = (double)(uint32_t)own[s].z; d[s][3] = (double)(uint32_t)own[s].w;
+    d[s][0] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].x); d[s][1] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].y);
+    d[s][2] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].z); d[s][3] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].w);
 #pragma unroll
     for (int k = 0; k < 4; ++k) ir[s][k] = __dmul_rn(diag, d[s][k]);
     e[s] = blk[s].advance(1);
