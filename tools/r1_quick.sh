@@ -9,8 +9,8 @@ for l in sys.stdin:
 : > gpurun_out/quick.log
 run() { echo "== $*" >> gpurun_out/quick.log; timeout 160 $B "$@" 2>&1 | python -c "$P" >> gpurun_out/quick.log; }
 run
-run --gen-dual 1
-run --gen-dual 1 --gen-warps 12
-run --gen-dual 1 --nnz 16
-run --gen-dual 1 --nnz 51
-run --gen-dual 1 --gen-warps 12 --nnz 51
+run --gen-warps 20
+run --gen-warps 12
+run --nnz 16
+run --nnz 51
+python bench.py > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err
