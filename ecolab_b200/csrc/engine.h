@@ -116,8 +116,8 @@ class Engine {
   void last_kernel_config(int* grid, int* block, int* smem) const {
     *grid = last_grid_; *block = last_block_; *smem = last_smem_;
   }
-  // tuning knobs (bench/profiling): 0 = auto.  gen_variant: consumer warps of the generate pipeline (16/24/31);
-  // gen_stages: shared-memory tile buffers
+  // tuning knobs (bench/profiling): 0 = auto.  gen_variant: consumer warps of the generate pipeline (12/16/20 with two
+  // blocks per warp, 24/31 with one); gen_stages: shared-memory tile buffers; mig_variant: tiles a migrate warp spans
   int gen_variant = 0;
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory

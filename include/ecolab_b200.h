@@ -166,7 +166,9 @@ int eco_append_species(eco_model* m, const uint32_t* birth_cells, size_t n);
 void eco_array_urand_seed(int seed);
 void eco_array_grand_reset(void);
 
-/* tuning / profiling knobs: "gen_threads" (256/512/1024, 0=auto), "mig_variant",
+/* tuning / profiling knobs (0 = automatic): "gen_threads" (consumer warps of generate(1): 12/16/20 with two blocks
+ * per warp, 24/31 with one; threads/32 of the multi-step kernel), "gen_dual" (1 / -1: force two / one block per consumer
+ * warp), "gen_stages", "gen_nobsmem", "mig_variant" (tiles a migrate warp spans: 1/2/4/8), "gen_dense", "dense_slices",
  * "timing" (1 = record a CUDA-event pair around every generate/migrate launch, 0 = off and reset) */
 int eco_set_tuning(eco_model* m, const char* knob, int value);
 /* device time per kernel kind since timing was switched on: out = {generate_ms, generate_launches,

@@ -94,6 +94,19 @@ def test_migrate_bit_exact_and_conserves(oracle_mod, gpu, grid, nsp, k):
         assert m.last_mig_tstep() == m.tstep()
 
 
+@pytest.mark.parametrize("grid,nsp,k", [((250, 3), 1000, 3), ((256, 4), 37, 3), ((120, 5), 300, 2), ((64, 7), 2000, 1)])
+@pytest.mark.parametrize("span", [2, 4, 8])
+def test_migrate_warp_spans(oracle_mod, gpu, grid, nsp, k, span):
+    """migrate with a warp spanning 2/4/8 adjacent tiles (knob mig_variant; the engine falls back to the widest span
+    the tile count allows): same bits, ragged last tiles included."""
+    o, m, grid = pair(oracle_mod, gpu, grid, nsp, k, mig=0.11)
+    m.set_tuning("mig_variant", span)
+    for it in range(2):
+        o.generate(1); m.generate(1)
+        assert m.migrate() == o.migrate()
+        assert np.array_equal(m.density_array(), o.get_density_all())
+
+
 def test_migrate_cap_and_per_species_rates(oracle_mod, gpu):
     """cm = min(dt*migration, 1/maxNbrs) (:626-629): huge rates are capped so a cell is never overdrawn."""
     grid, nsp = (9, 6), 11
