@@ -162,7 +162,7 @@ def build_model(E, args, nx, ny, comm, device, stream):
     import ctypes as C
     from helpers import SCALARS
     m = E.SpatialModel(device, comm)
-    E._cabi.check(m._L.eco_set_stream(m._h, C.c_void_p(stream.cuda_stream)))
+    m.set_stream(stream)
     p = synth_params(args.nsp, args.nnz)
     for k, v in SCALARS.items():
         getattr(m, k)(v)
@@ -342,7 +342,7 @@ def run_dense(args):
     nx, ny, nsp = args.nx or 256, args.ny or 256, args.nsp if args.nsp != 1024 else 8192
     rng = np.random.default_rng(10)
     m = E.SpatialModel(0, None)
-    E._cabi.check(m._L.eco_set_stream(m._h, C.c_void_p(stream.cuda_stream)))
+    m.set_stream(stream)
     for k, v in SCALARS.items():
         getattr(m, k)(v)
     m.species(np.arange(nsp, dtype=np.int32))

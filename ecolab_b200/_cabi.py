@@ -68,6 +68,7 @@ SIGNATURES = {
     "eco_checkpoint": [_vp, _cp],
     "eco_restart": [_vp, _cp],
     "eco_migrate_local": [_vp, _P(_u64)],
+    "eco_migrate_local_async": [_vp, _P(_vp)],
     "eco_halo_ptrs": [_vp, _P(_vp), _P(_vp), _P(_vp), _P(_vp), _P(_sz)],
     "eco_ipc_export": [_vp, _vp, _P(_sz), _P(_sz)],
     "eco_ipc_import": [_vp, _vp, _P(_vp)],

@@ -46,6 +46,7 @@ class Engine {
 
   void set_stream(void* s);
   void* stream() const { return (void*)stream_; }
+  void* total_dev() const { return (void*)d_total_; }   // device copy of the last migrate's sum |delta| (uint64)
   void sync();
 
   // density access, cells addressed by LOCAL index x + nx*(y-y0)

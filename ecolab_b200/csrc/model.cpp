@@ -180,7 +180,7 @@ struct eco_model {
     tstep += niter;
   }
 
-  uint64_t migrate_local() {
+  uint64_t migrate_local(bool wait = true) {
     check_sizes(true);
     const size_t n = nsp();
     std::vector<double> cm(n);
@@ -190,7 +190,7 @@ struct eco_model {
       cm[s] = mm > cap ? cap : mm;                                  // :629
     }
     salt_t = tstep;
-    const uint64_t total = n ? eng.migrate(cm.data()) : 0;
+    const uint64_t total = n ? eng.migrate(cm.data(), wait) : 0;
     last_mig_tstep = tstep;
     return total;
   }
@@ -726,6 +726,14 @@ int eco_migrate_local(eco_model* m, uint64_t* total) {
   need(m);
   const uint64_t t = m->migrate_local();
   if (total) *total = t;
+  ECO_CATCH
+}
+int eco_migrate_local_async(eco_model* m, void** total_dev) {
+  ECO_TRY
+  need(m);
+  if (!m->nsp()) throw std::runtime_error("migrate_local_async: no species");
+  m->migrate_local(false);
+  if (total_dev) *total_dev = m->eng.total_dev();
   ECO_CATCH
 }
 int eco_condense(eco_model* m, unsigned* removed) {

@@ -129,6 +129,10 @@ def dist_migrate(ops, comm):
     if t is not None:
         comm.sendrecv_rows(*t)
         ops.halo_done()
+    dev_total = ops.migrate_local_device() if comm.backend == "nccl" and hasattr(ops, "migrate_local_device") else None
+    if dev_total is not None:   # all-reduce enqueued behind the kernel: one host synchronisation per migrate, at the end
+        comm.dist.all_reduce(dev_total, op=comm.dist.ReduceOp.SUM, group=comm.group)
+        return int(dev_total.cpu()[0]) // 2
     return comm.allreduce_sum(ops.migrate_local()) // 2   # :667-672, :702
 
 
@@ -160,8 +164,9 @@ def dist_mutate(ops, comm):
 class _DevMem:
     """Expose a raw device range to torch through __cuda_array_interface__ (no copy)."""
 
-    def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+    def __init__(self, ptr, nbytes, typestr="<i4"):
+        self.__cuda_array_interface__ = {"shape": (nbytes // int(typestr[2:]),), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2}
 
 
 class SpatialModel(EcolabModelBase):
@@ -239,12 +244,36 @@ class SpatialModel(EcolabModelBase):
             return None
         dev = torch.device("cuda", self._device)
         T = lambda p: torch.as_tensor(_DevMem(p.value, nb.value), device=dev)   # noqa: E731
-        self.syncThreads()   # generate ran on the engine's stream; NCCL is enqueued on torch's
+        if not self._on_torch_stream():
+            self.syncThreads()   # generate ran on the engine's own stream; NCCL is ordered after torch's current stream
         return T(st), T(rt), T(sb), T(rb)
 
     def halo_done(self):
         import torch
-        torch.cuda.current_stream(torch.device("cuda", self._device)).synchronize()
+        if not self._on_torch_stream():
+            torch.cuda.current_stream(torch.device("cuda", self._device)).synchronize()
+
+    def set_stream(self, torch_stream):
+        """Run this model's kernels on a torch stream (eco_set_stream).  When it is also torch's CURRENT stream the
+        multi-GPU driver needs no host synchronisation between kernels and collectives: NCCL orders itself after the
+        current stream and the current stream waits for NCCL (work.wait())."""
+        check(self._L.eco_set_stream(self._h, C.c_void_p(torch_stream.cuda_stream)))
+        self._stream_handle = int(torch_stream.cuda_stream)
+
+    def _on_torch_stream(self):
+        import torch
+        h = getattr(self, "_stream_handle", None)
+        return h is not None and h == int(torch.cuda.current_stream(torch.device("cuda", self._device)).cuda_stream)
+
+    def migrate_local_device(self):
+        """migrate on the owned slab without waiting; returns the device-resident int64[1] sum |delta| (not halved), or
+        None when the kernels do not run on torch's current stream (the caller then uses migrate_local)."""
+        import torch
+        if not self._on_torch_stream() or not int(self._scalar("nsp")):
+            return None
+        p = C.c_void_p()
+        check(self._L.eco_migrate_local_async(self._h, C.byref(p)))
+        return torch.as_tensor(_DevMem(p.value, 8, "<i8"), device=torch.device("cuda", self._device))
 
     def migrate_local(self):
         t = C.c_uint64()

@@ -141,6 +141,10 @@ int eco_restart(eco_model* m, const char* file);
 /* migrate on the owned slab using the ghost rows (or peer rows) as neighbours;
  * *abs_delta_sum = sum |delta| over owned cells, NOT halved. (:631-664) */
 int eco_migrate_local(eco_model* m, uint64_t* abs_delta_sum);
+/* the same without waiting for the kernel: *total_dev = device address of the uint64 sum |delta| (valid on the model's
+ * stream after the launch), so the all-reduce of SpatialModel::migrate's return value (:667-672) can be enqueued
+ * behind the kernel without a host round trip */
+int eco_migrate_local_async(eco_model* m, void** total_dev);
 /* device pointers + byte size of the two boundary rows to send and the two ghost rows to fill */
 int eco_halo_ptrs(eco_model* m, void** send_top, void** send_bottom, void** recv_top, void** recv_bottom,
                   size_t* row_bytes);
