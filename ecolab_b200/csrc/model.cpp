@@ -120,9 +120,13 @@ struct eco_model {
     };
     if (eng.nsp() > n) bad("cell density", eng.nsp());
     grow_engine(n);
+    // migrate reads only `migration` (:626-629): models/migration_test.py sets nothing else before calling it
+    if (need_migration) {
+      if (migration.size() != n) bad("migration", migration.size());
+      return;
+    }
     if (repro_rate.size() != n) bad("repro_rate", repro_rate.size());
     if (diag.size() != n) bad("interaction.diag", diag.size());
-    if (need_migration && migration.size() != n) bad("migration", migration.size());
     if (row.size() != val.size() || col.size() != val.size())
       throw std::runtime_error("inconsistent model: interaction.row/col/val differ in length");
   }
@@ -201,6 +205,7 @@ struct eco_model {
     if (ncells != ncells_local()) throw std::runtime_error("step_host: cell count differs from the grid");
     if (tstep == 0) makeConsistent();
     grow_engine(std::max(ns, nsp()));
+    check_sizes(false);
     check_sizes(true);
     if (ns != nsp()) throw std::runtime_error("step_host: species count differs from the model");
     upload();
