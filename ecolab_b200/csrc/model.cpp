@@ -608,6 +608,9 @@ int eco_set_density(eco_model* m, size_t cell, const int32_t* d, size_t n) {
   const size_t lc = m->local_cell(cell);
   for (size_t i = 0; i < n; ++i)
     if (d[i] < 0) throw std::runtime_error("density must be non-negative (reference asserts density>=0, models/ecolab_model.cc:108)");
+  // the panmictic model IS its one cell: assigning its density replaces the array, shorter or longer (pred-prey.py
+  // re-initialises the global object with 2 species after any earlier run); a spatial cell is padded to the model's count
+  if (m->panmictic && std::max(n, m->nsp()) < m->eng.nsp()) m->eng.resize_species((uint32_t)std::max(n, m->nsp()));
   m->grow_engine(std::max(n, m->nsp()));
   m->eng.set_density(lc, d, n);
   ECO_CATCH

@@ -194,3 +194,62 @@ def test_panmictic_ecolab_py(oracle_mod, mods, gpu):
         plot.plot("No. species", m.tstep(), len(m.species))
         assert abs(m.connectivity() - o.connectivity()) <= 1e-15 * max(1.0, abs(o.connectivity()))
     assert m.tstep() == 600
+
+
+def test_pred_prey_py(oracle_mod, mods):
+    """pred-prey.py: two species with ids [1, 2], everything set member by member, generate() with its default niter,
+    density()._properties read every step; no migration array, no mutate, no condense."""
+    em, eco, GUI, plot = mods
+    m = em.panmictic_ecolab
+    m.tstep(0)
+    m.species([1, 2])
+    m.density([100, 100])
+    m.create([0, 0])
+    m.repro_rate([.1, -.1])
+    m.interaction.diag([-.0001, -1e-5])
+    m.interaction.val([-0.001, 0.001])
+    m.interaction.row([0, 1])
+    m.interaction.col([1, 0])
+    m.mutation([.01, .01])
+    m.sp_sep(.1); m.repro_min(-.1); m.repro_max(.1); m.odiag_min(-1e-3); m.odiag_max(1e-3); m.mut_max(.01)
+    m.seed(10)
+    p = _params_of(m)
+    p["migration"] = np.zeros(2)
+    o = load_oracle(oracle_mod, p, np.array([m.density()], dtype=np.int32), None, scalars=_scalars_of(m))
+    for _ in range(60):
+        m.generate(); o.generate(1)
+        density = m.density()._properties
+        GUI.statusBar.configure(text=f"t={m.tstep()} n={density}")
+        plot.plot("density", m.tstep(), density)
+        assert m.density() == o.get_density(0).tolist()
+    assert m.tstep() == 60 and m.species() == [1, 2]
+
+
+def test_fragmentation_pump_py(oracle_mod, mods, gpu):
+    """fragmentation_pump.py:63-80: the migration rates are switched off (all 0) and back on (1e-3) between epochs while the
+    generate(100); mutate(); migrate(); condense() loop keeps running."""
+    em, eco, GUI, plot = mods
+    m = em.spatial_ecolab
+    O = oracle_mod
+    nsp, nx, ny = 60, 3, 2
+    m.fixMigration(True); m.fixMutation(False)
+    _init_spatial(m, eco, nsp, nx, ny, mut_max=1e-3, migration=1e-3, odiag=1e-4, seed=4)
+    o = load_oracle(O, _params_of(m), _dens(m, nx, ny), (nx, ny), scalars=_scalars_of(m))
+    o.set("fixMigration", 1)
+    saved = None
+    for it in range(6):
+        m.generate(100); o.generate(100)
+        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        O.srand(it); O.reset_grand(); o.mutate()
+        if it == 2:                                    # half epoch: fragment the landscape
+            saved = m.migration()
+            m.migration(len(m.species) * [0]); o.set("migration", np.zeros(len(m.species)))
+        if it == 4:                                    # epoch: reconnect it
+            m.migration(len(m.species) * [1e-3]); o.set("migration", np.full(len(m.species), 1e-3))
+        mv = m.migrate()
+        assert mv == o.migrate()
+        if it in (2, 3):
+            assert mv == 0
+        assert m.condense() == o.condense()
+        assert np.array_equal(_dens(m, nx, ny), o.get_density_all())
+    assert saved is not None and len(saved) > 0 and all(x == 1e-3 for x in saved)
