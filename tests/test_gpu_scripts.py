@@ -253,3 +253,45 @@ def test_fragmentation_pump_py(oracle_mod, mods, gpu):
         assert m.condense() == o.condense()
         assert np.array_equal(_dens(m, nx, ny), o.get_density_all())
     assert saved is not None and len(saved) > 0 and all(x == 1e-3 for x in saved)
+
+
+def test_spatial_ecolab_sh(mods):
+    """test/00/spatial_ecolab.sh:18-77 as a fresh process would run it: parameters BEFORE setGrid, generate() with its
+    default argument, every cell changes, migrate() conserves every species' total."""
+    em, eco, GUI, plot = mods
+    m = em._Lazy(em._make_spatial)          # a fresh process-lifetime object, as in a new interpreter
+    random.seed(1)
+    nsp = 30
+    m.species(range(nsp))
+    m.repro_min(-.1); m.repro_max(.1); m.odiag_min(-1e-5); m.odiag_max(1e-5)
+    m.repro_rate(_rand_list(nsp, m.repro_min(), m.repro_max()))
+    m.interaction.diag(_rand_list(nsp, -1e-3, -1e-3))
+    m.random_interaction(3, 0)
+    m.interaction.val(_rand_list(len(m.interaction.val), m.odiag_min(), m.odiag_max()))
+    m.mut_max(1e-4); m.sp_sep(0.1)
+    m.mutation(nsp * [m.mut_max()])
+    m.migration(nsp * [1e-5])
+    m.setGrid(2, 2)
+    initd = nsp * [100]
+    for i, j in ((0, 0), (0, 1), (1, 0), (1, 1)):
+        m.cell(i, j).density(initd)
+    m.distributeObjects()
+    m.generate()
+    m.gather()
+    for i, j in ((0, 0), (0, 1), (1, 0), (1, 1)):
+        assert m.cell(i, j).density() != initd
+    n0 = nsp * [0]
+    for i in range(2):
+        for j in range(2):
+            d = m.cell(i, j).density()
+            for k in range(nsp):
+                n0[k] += d[k]
+    m.tstep(m.tstep() + 999)                # so that dt*migration really moves individuals (1e-5 * 1000 * ~100 >= 1)
+    moved = m.migrate()
+    n1 = nsp * [0]
+    for i in range(2):
+        for j in range(2):
+            d = m.cell(i, j).density()
+            for k in range(nsp):
+                n1[k] += d[k]
+    assert n0 == n1 and moved >= 0
