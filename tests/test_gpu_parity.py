@@ -107,6 +107,29 @@ def test_migrate_warp_spans(oracle_mod, gpu, grid, nsp, k, span):
         assert np.array_equal(m.density_array(), o.get_density_all())
 
 
+def test_migrate_extreme_densities(oracle_mod, gpu):
+    """Densities at the top of the int32 range next to empty cells: the 2^52+n trick and the flux sums stay exact, totals
+    are conserved, nothing goes negative (the cap 1/maxNbrs guarantees a cell is never overdrawn, :626-629)."""
+    grid, nsp = (37, 5), 9
+    p = synth(nsp, 2, 6)
+    p["migration"] = np.array([1.0, 0.25, 0.2499999, 0.1, 1e-9, 0.5, 0.05, 0.24, 3.0])
+    rng = np.random.default_rng(11)
+    d = np.zeros((grid[0] * grid[1], nsp), dtype=np.int32)
+    hot = rng.random(d.shape) < 0.3
+    d[hot] = rng.integers(2 ** 31 - 1000, 2 ** 31 - 2, size=int(hot.sum()), dtype=np.int64).astype(np.int32)
+    d[rng.random(d.shape) < 0.1] = 2 ** 31 - 2
+    o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
+    o.set("tstep", 1); m.tstep(1)            # dt = 1 since last_mig_tstep = 0
+    for span in (0, 2, 4):
+        m.set_tuning("mig_variant", span)
+        before = m.species_totals()
+        assert m.migrate() == o.migrate()
+        got = m.density_array()
+        assert np.array_equal(got, o.get_density_all()) and (got >= 0).all()
+        assert np.array_equal(m.species_totals(), before)
+        o.set("tstep", int(o.get("tstep")) + 1); m.tstep(m.tstep() + 1)
+
+
 def test_migrate_cap_and_per_species_rates(oracle_mod, gpu):
     """cm = min(dt*migration, 1/maxNbrs) (:626-629): huge rates are capped so a cell is never overdrawn."""
     grid, nsp = (9, 6), 11
