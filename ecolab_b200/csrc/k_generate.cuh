@@ -97,17 +97,21 @@ __device__ __forceinline__ double cvt_n(int n) {
 // independent twin to hide its latency.  int -> double runs on the conversion (XU) pipe, which is otherwise idle;
 // multiply and accumulate stay two individually rounded FP64 operations (no contraction: -fmad=false).
 template <int TW, bool BSMEM, int NS, int NT>
-__device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (&e)[NS], double (&ir)[NS][4]) {
-  uint4 w[NS][NT];
-  int4 g[NS][NT];
+__device__ __forceinline__ void gen_load_recs(const RecCol<TW, BSMEM> (&e)[NS], int first, uint4 (&w)[NS][NT]) {
 #pragma unroll
   for (int s = 0; s < NS; ++s)
 #pragma unroll
-    for (int j = 0; j < NT; ++j) w[s][j] = e[s].ld(j);
+    for (int j = 0; j < NT; ++j) w[s][j] = e[s].ld(first + j);
+}
+template <int NS, int NT>
+__device__ __forceinline__ void gen_gather(uint32_t lp, const uint4 (&w)[NS][NT], int4 (&g)[NS][NT]) {
 #pragma unroll
   for (int s = 0; s < NS; ++s)
 #pragma unroll
     for (int j = 0; j < NT; ++j) g[s][j] = lds128i(lp + w[s][j].z);
+}
+template <int NS, int NT>
+__device__ __forceinline__ void gen_accumulate(const uint4 (&w)[NS][NT], const int4 (&g)[NS][NT], double (&ir)[NS][4]) {
 #pragma unroll
   for (int j = 0; j < NT; ++j)
 #pragma unroll
@@ -125,6 +129,51 @@ __device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (
         ir[s][3] = __dadd_rn(ir[s][3], __dmul_rn(v, cvt_n<false>(g[s][j].w)));
       }
     }
+}
+template <int TW, bool BSMEM, int NS, int NT>
+__device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (&e)[NS], double (&ir)[NS][4]) {
+  uint4 w[NS][NT];
+  int4 g[NS][NT];
+  gen_load_recs<TW, BSMEM, NS, NT>(e, 0, w);
+  gen_gather<NS, NT>(lp, w, g);
+  gen_accumulate<NS, NT>(w, g, ir);
+}
+
+// Long rows (W >= 8), four terms at a time: the records of the NEXT four terms are requested before the arithmetic of
+// the current four, so their latency (L2 when the stream does not fit in shared memory: ~300 cycles, it was the top
+// stall of the 51-term profile) hides behind ~60 FP64 operations.  Two record buffers alternate: no register copies.
+template <int TW, bool BSMEM, int NS>
+__device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSMEM> (&e)[NS], uint32_t& W, double (&ir)[NS][4]) {
+  uint4 wa[NS][4], wb[NS][4];
+  int4 g[NS][4];
+  gen_load_recs<TW, BSMEM, NS, 4>(e, 0, wa);
+  while (W >= 12) {                       // wa holds terms [0,4) of e; at least 8 more follow
+    gen_gather<NS, 4>(lp, wa, g);
+    gen_load_recs<TW, BSMEM, NS, 4>(e, 4, wb);
+    gen_accumulate<NS, 4>(wa, g, ir);
+    gen_gather<NS, 4>(lp, wb, g);
+    gen_load_recs<TW, BSMEM, NS, 4>(e, 8, wa);
+    gen_accumulate<NS, 4>(wb, g, ir);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) e[s] = e[s].advance(8);
+    W -= 8;
+  }
+  // 4 <= W < 12, wa holds the next four
+  gen_gather<NS, 4>(lp, wa, g);
+  if (W >= 8) {
+    gen_load_recs<TW, BSMEM, NS, 4>(e, 4, wb);
+    gen_accumulate<NS, 4>(wa, g, ir);
+    gen_gather<NS, 4>(lp, wb, g);
+    gen_accumulate<NS, 4>(wb, g, ir);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) e[s] = e[s].advance(8);
+    W -= 8;
+  } else {
+    gen_accumulate<NS, 4>(wa, g, ir);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) e[s] = e[s].advance(4);
+    W -= 4;
+  }
 }
 
 // NS warp-ops: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of one species row each.
@@ -145,6 +194,9 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
 #pragma unroll
     for (int k = 0; k < 4; ++k) ir[s][k] = __dmul_rn(diag, d[s][k]);
     e[s] = blk[s].advance(1);
+  }
+  if constexpr (NS == 1) {
+    if (W >= 8) gen_terms_pipelined<TW, BSMEM, NS>(lp, e, W, ir);   // leaves W < 4
   }
   for (; W >= 4; W -= 4) {
     gen_terms<TW, BSMEM, NS, 4>(lp, e, ir);

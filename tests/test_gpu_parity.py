@@ -20,6 +20,8 @@ SHAPES = [
     (None, 2, 1), (None, 100, 3), (None, 1, 0), (None, 1023, 5),
     ((1, 1), 7, 2), ((2, 2), 30, 3), ((8, 5), 37, 3), ((33, 3), 64, 16), ((64, 2), 9, 8), ((70, 9), 129, 3),
     ((31, 1), 5, 0), ((1, 40), 12, 4),
+    # long rows: the software-pipelined term loop (W >= 8) with every remainder, stream in shared memory and not
+    (None, 50, 8), (None, 50, 9), ((5, 5), 80, 11), ((9, 2), 64, 12), ((20, 3), 200, 51), ((18, 2), 1100, 23),
 ]
 
 
