@@ -61,9 +61,12 @@ struct RecCol {
 };
 
 // Philox4x32-10 with the key schedule taken from kernel parameters (constant bank operands, no key arithmetic)
+#ifndef ECO_PHILOX_ROUNDS
+#define ECO_PHILOX_ROUNDS 10   // the RNG contract (k_common.cuh, oracle); other values exist only to price the contract
+#endif
 __device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t (&rk)[20]) {
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < ECO_PHILOX_ROUNDS; ++r) {
     const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
     const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
     const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk[2 * r];
