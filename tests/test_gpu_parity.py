@@ -335,3 +335,55 @@ def test_empty_model_is_harmless(gpu):
     assert m.migrate() == 0 and m.condense() == 0
     m.mutate()
     assert m.nsp() == [0] * 16
+
+
+@pytest.mark.parametrize("nsp,conn,sigma", [(100, 3, 0.0), (64, 5, 1.5), (30, 0, 0.0), (200, 10, 3.0), (8, 7, 0.0)])
+def test_random_interaction_matches_oracle(oracle_mod, gpu, nsp, conn, sigma):
+    """ModelData::random_interaction (:43-47 -> sparse_mat::init_rand, include/sparse_mat.h:88-111): same libc stream,
+    same pattern -- row sizes ~ N(conn, sigma), distinct columns, self-links dropped, val zero-filled."""
+    O = oracle_mod
+    p = synth(nsp, 0, 2)
+    o = load_oracle(O, p, densities(1, nsp, 2), None)
+    m = load_gpu(gpu, p, densities(1, nsp, 2), None)
+    O.srand(77); O.reset_grand(); o.random_interaction(conn, sigma)
+    O.srand(77); gpu.lib().eco_array_grand_reset(); m.random_interaction(conn, sigma)
+    for k in ("row", "col", "val"):
+        assert list(getattr(m.interaction, k)()) == list(o.get("interaction." + k)), k
+    row, col = np.array(m.interaction.row()), np.array(m.interaction.col())
+    assert (row != col).all() and len(m.interaction.val) == len(row) and (np.array(m.interaction.val()) == 0).all()
+    if len(row):
+        assert row.max() < nsp and col.max() < nsp
+        assert len(set(zip(row.tolist(), col.tolist()))) == len(row)      # distinct links
+
+
+def test_panmictic_observables(oracle_mod, gpu):
+    """PanmicticModel::lifetimes (:474-490) against the oracle; mutantConnectivity / extinctionConnectivity (:493-516)
+    against the formulas of the reference restated with numpy."""
+    O = oracle_mod
+    nsp = 80
+    p = synth(nsp, 4, 12, mut=2e-3)
+    p["repro_rate"][::3] = -0.3                      # a third of the species dies out quickly
+    d = densities(1, nsp, 12)
+    scal = dict(SCALARS, mut_max=2e-3)
+    o = load_oracle(O, p, d, None, scalars=scal); m = load_gpu(gpu, p, d, None, scalars=scal)
+    seen = 0
+    for it in range(8):
+        before = len(m.species)
+        o.generate(20); m.generate(20)
+        O.srand(it); O.reset_grand(); o.mutate()
+        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        lt_g, lt_o = list(m.lifetimes()), o.lifetimes().tolist()
+        assert lt_g == lt_o
+        seen += len(lt_g)
+        dens = np.array(m.density()); ns = len(dens)
+        row, col = np.array(m.interaction.row(), dtype=np.int64), np.array(m.interaction.col(), dtype=np.int64)
+        val, diag = np.array(m.interaction.val()), np.array(m.interaction.diag())
+        w = val * val / (diag[row] * diag[col]) if len(row) else np.zeros(0)
+        want_m = w[(row > before) | (col > before)].sum() / ((ns - before) * (ns - 1)) if ns > before else 0.0
+        dead = int((dens == 0).sum())
+        want_e = w[(dens[row] == 0) | (dens[col] == 0)].sum() / (dead * (ns - 1)) if dead else 0.0
+        assert m.mutantConnectivity(before) == pytest.approx(want_m, rel=1e-12, abs=1e-300)
+        assert m.extinctionConnectivity() == pytest.approx(want_e, rel=1e-12, abs=1e-300)
+        assert m.condense() == o.condense()
+        assert m.density() == o.get_density(0).tolist()
+    assert seen > 0      # some species did live and die
