@@ -323,7 +323,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
   const uint32_t tiles_s = smem_u32(tiles) + 16u * q, strm_s = smem_u32(s_stream) + 16u * rr, boff_s = smem_u32(s_boff);
   const uint32_t uslots = p.uslots;
   if constexpr (NS == 2) {
-    const uint32_t npairs = (nblocks + 1) / 2, npm = npairs % NW;
+    const uint32_t npf = nblocks / 2, npairs = (nblocks + 1) / 2, npm = npairs % NW;   // full pairs; units dealt round-robin
     const uint32_t W = uslots - 1u, blk_bytes = uslots * (R * 16u);
     uint32_t first = warp, stage = 0, round = 0;
     for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
@@ -333,26 +333,37 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       asm volatile("" : "+l"(gl));
       const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
       const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
-      for (uint32_t pr = first; pr < npairs; pr += NW) {
+      uint32_t pr = first;
+      for (; pr < npf; pr += NW) {                     // full pairs: no tail case inside the loop
         const uint32_t b0 = 2 * pr;
-        const bool has1 = b0 + 1 < nblocks;            // warp-uniform; false only for the last pair of an odd block count
-        const uint32_t b1 = has1 ? b0 + 1 : b0;
         const uint32_t a0 = lp + b0 * (R * TW * 4u) + rr * (TW * 4u);
         int4 own[2];
         own[0] = lds128i(a0);
-        own[1] = lds128i(a0 + (b1 - b0) * (R * TW * 4u));
+        own[1] = lds128i(a0 + R * TW * 4u);
         if (!__any_sync(FULL, (own[0].x | own[0].y | own[0].z | own[0].w | own[1].x | own[1].y | own[1].z | own[1].w) != 0)) continue;
         RecCol<TW, BSMEM> blk[2];
         blk[0].a = strm_s + b0 * blk_bytes; blk[0].p = p.stream + (size_t)b0 * uslots * R + rr;
-        blk[1].a = strm_s + b1 * blk_bytes; blk[1].p = p.stream + (size_t)b1 * uslots * R + rr;
+        blk[1].a = blk[0].a + blk_bytes;    blk[1].p = blk[0].p + (size_t)uslots * R;
         double x[2][4];
         gen_x_n<TW, BSMEM, 2>(lp, own, blk, W, x);
-        const uint32_t row0 = b0 * R + rr, row1 = b1 * R + rr;
-        const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row1, (uint32_t)p.t0, p.rk);
+        const uint32_t row0 = b0 * R + rr;
+        const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row0 + R, (uint32_t)p.t0, p.rk);
         int4 o0, o1;
         round4x2(x, u0, u1, o0, o1);
         __stcs(reinterpret_cast<int4*>(gl + b0 * (R * TW)), o0);
-        if (has1) __stcs(reinterpret_cast<int4*>(gl + b1 * (R * TW)), o1);
+        __stcs(reinterpret_cast<int4*>(gl + (b0 + 1) * (R * TW)), o1);
+      }
+      if (pr == npf && (nblocks & 1u)) {               // odd block count: the last block alone, by the warp whose turn it is
+        const uint32_t b = nblocks - 1u, row = b * R + rr;
+        const int4 own = lds128i(lp + b * (R * TW * 4u) + rr * (TW * 4u));
+        if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
+          RecCol<TW, BSMEM> blk;
+          blk.a = strm_s + b * blk_bytes; blk.p = p.stream + (size_t)b * uslots * R + rr;
+          double x[4];
+          gen_x<TW, BSMEM>(lp, own, blk, W, x);
+          const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
+          __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
+        }
       }
       first += NW - npm;
       if (first >= NW) first -= NW;
