@@ -333,10 +333,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       asm volatile("" : "+l"(gl));
       const uint32_t yl = tile_id / p.L.ntx, tx = tile_id - yl * p.L.ntx;
       const uint32_t xq = tx * (TW / 4) + q, yg = p.L.y0 + yl;
+      uint32_t lpo = lp + rr * (TW * 4u);              // this lane's row inside block 0
+      asm volatile("" : "+r"(lpo));                    // keep it: the compiler would rebuild it from the lane id per pair
       uint32_t pr = first;
       for (; pr < npf; pr += NW) {                     // full pairs: no tail case inside the loop
         const uint32_t b0 = 2 * pr;
-        const uint32_t a0 = lp + b0 * (R * TW * 4u) + rr * (TW * 4u);
+        const uint32_t a0 = lpo + b0 * (R * TW * 4u);
         int4 own[2];
         own[0] = lds128i(a0);
         own[1] = lds128i(a0 + R * TW * 4u);
