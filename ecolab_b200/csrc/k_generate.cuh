@@ -12,6 +12,8 @@
 //     ir = diag*n ; ir = ir + val_j*n[col_j] (j ascending) ; x = n + n*(r + ir), every operation individually rounded.
 //
 #pragma once
+#include <type_traits>
+
 #include "k_common.cuh"
 
 namespace eco {
@@ -182,7 +184,8 @@ __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSME
 // NS warp-ops: the four pre-rounding values x = n + n*(r + ir) of this lane's cells of one species row each.
 // `lp` = shared address of the tile + 16*quad; `own` = the lane's own densities; `blk` = this lane's record column
 // of the block (header first); W = terms per row (warp-uniform, the same for all NS blocks).
-template <int TW, bool BSMEM, int NS>
+// WC >= 0: the width is the compile-time constant WC (<= 4) and W is ignored -- no width dispatch per warp-op.
+template <int TW, bool BSMEM, int NS, int WC = -1>
 __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], const RecCol<TW, BSMEM> (&blk)[NS], uint32_t W,
                                         double (&x)[NS][4]) {
   double d[NS][4], ir[NS][4], rr[NS];
@@ -198,6 +201,8 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     for (int k = 0; k < 4; ++k) ir[s][k] = __dmul_rn(diag, d[s][k]);
     e[s] = blk[s].advance(1);
   }
+  if constexpr (WC > 0) gen_terms<TW, BSMEM, NS, WC>(lp, e, ir);
+  if constexpr (WC >= 0) W = 0;
   if constexpr (NS == 1) {
     if (W >= 8) gen_terms_pipelined<TW, BSMEM, NS>(lp, e, W, ir);   // leaves W < 4
   }
@@ -325,6 +330,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
   if constexpr (NS == 2) {
     const uint32_t npf = nblocks / 2, npairs = (nblocks + 1) / 2, npm = npairs % NW;   // full pairs; units dealt round-robin
     const uint32_t W = uslots - 1u, blk_bytes = uslots * (R * 16u);
+    // the whole consumer loop once per compile-time row width (the width is the same for every block of a uniform stream)
+    auto consume = [&](auto wc) {
+    constexpr int WC = decltype(wc)::value;
     uint32_t first = warp, stage = 0, round = 0;
     for (uint32_t tile_id = blockIdx.x; tile_id < ntiles; tile_id += gridDim.x) {
       mbar_wait(full + stage, round & 1u);
@@ -347,7 +355,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
         blk[0].a = strm_s + b0 * blk_bytes; blk[0].p = p.stream + (size_t)b0 * uslots * R + rr;
         blk[1].a = blk[0].a + blk_bytes;    blk[1].p = blk[0].p + (size_t)uslots * R;
         double x[2][4];
-        gen_x_n<TW, BSMEM, 2>(lp, own, blk, W, x);
+        gen_x_n<TW, BSMEM, 2, WC>(lp, own, blk, W, x);
         const uint32_t row0 = b0 * R + rr;
         const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row0 + R, (uint32_t)p.t0, p.rk);
         int4 o0, o1;
@@ -372,6 +380,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       __syncwarp();
       if (lane == 0) mbar_arrive(empty + stage);
       if (++stage == S) { stage = 0; ++round; }
+    }
+    };
+    switch (W) {   // kernel-uniform
+      case 3: consume(std::integral_constant<int, 3>{}); break;   // the scripts' random_interaction(3,0)
+      case 2: consume(std::integral_constant<int, 2>{}); break;
+      case 4: consume(std::integral_constant<int, 4>{}); break;
+      default: consume(std::integral_constant<int, -1>{}); break;
     }
     return;
   }
