@@ -350,7 +350,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
         int4 own[2];
         own[0] = lds128i(a0);
         own[1] = lds128i(a0 + R * TW * 4u);
+#ifndef ECO_GEN_NOSKIP
         if (!__any_sync(FULL, (own[0].x | own[0].y | own[0].z | own[0].w | own[1].x | own[1].y | own[1].z | own[1].w) != 0)) continue;
+#endif
         RecCol<TW, BSMEM> blk[2];
         blk[0].a = strm_s + b0 * blk_bytes; blk[0].p = p.stream + (size_t)b0 * uslots * R + rr;
         blk[1].a = blk[0].a + blk_bytes;    blk[1].p = blk[0].p + (size_t)uslots * R;
