@@ -16,14 +16,14 @@
 #define ECO_MIG_MINB 2     // resident CTAs per SM the register budget is set for (2 x 256 threads -> up to 128 registers)
 #endif
 #ifndef ECO_MIG_NB
-#define ECO_MIG_NB 4       // grid rows a warp keeps in flight in registers.  Measured on C3 (ms): NB/CTAs per SM =
-                           // 2/4: 2.03 (spills)  2/3: 1.68  3/3: 2.03 (spills)  3/2: 1.73  4/2: 1.63  6/2: 1.89  8/1: 2.04
+#define ECO_MIG_NB 5       // grid rows a warp keeps in flight in registers.  Measured on C3 (ms): NB/CTAs per SM =
+                           // 2/4: 2.03 (spills)  2/3: 1.68  3/3: 2.03 (spills)  3/2: 1.73  4/2: 1.63  5/2: 1.61  6/2: 1.89  8/1: 2.04
 #endif
 #ifndef ECO_MIG_ALIAS
 #define ECO_MIG_ALIAS 1    // extra-cell loads unpredicated (measured on C3: 1.85 ms, predicated 1.96 ms)
 #endif
 #ifndef ECO_MIG_STCS
-#define ECO_MIG_STCS 0     // 1: streaming (evict-first) stores
+#define ECO_MIG_STCS 1     // 1: streaming (evict-first) stores (with 5 rows in flight: 1.60 vs 1.61 ms)
 #endif
 #ifndef ECO_MIG_LDCS
 #define ECO_MIG_LDCS 0     // 1: streaming loads of the lane's vector
