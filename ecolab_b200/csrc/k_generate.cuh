@@ -223,12 +223,12 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     for (int k = 0; k < 4; ++k) x[s][k] = __dadd_rn(d[s][k], __dmul_rn(d[s][k], __dadd_rn(rr[s], ir[s][k])));
 }
 
-template <int TW, bool BSMEM>
+template <int TW, bool BSMEM, int WC = -1>
 __device__ __forceinline__ void gen_x(uint32_t lp, const int4 own, const RecCol<TW, BSMEM>& blk, uint32_t W, double x[4]) {
   const int4 o1[1] = {own};
   const RecCol<TW, BSMEM> b1[1] = {blk};
   double x1[1][4];
-  gen_x_n<TW, BSMEM, 1>(lp, o1, b1, W, x1);
+  gen_x_n<TW, BSMEM, 1, WC>(lp, o1, b1, W, x1);
   x[0] = x1[0][0]; x[1] = x1[0][1]; x[2] = x1[0][2]; x[3] = x1[0][3];
 }
 
@@ -482,26 +482,38 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
     int32_t* src = buf0;
     int32_t* dst = buf1;
     uint32_t lp = buf0_s, lq = buf0_s + tile_bytes;   // shared addresses of src / dst (+ 16*quad)
-    for (uint32_t step = 0; step < p.niter; ++step) {
-      for (uint32_t b = warp; b < nblocks; b += nwarps) {
-        const uint32_t row = b * R + rr;
-        const int4 own = lds128i(lp + row * (TW * 4u));
-        int4 o = make_int4(0, 0, 0, 0);
-        if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
-          const uint32_t s0 = s_boff[b], s1 = s_boff[b + 1];
-          RecCol<TW, BSMEM> blk;
-          blk.a = strm_s + s0 * (R * 16u);
-          blk.p = strm + (size_t)s0 * R + rr;
-          double x[4];
-          gen_x<TW, BSMEM>(lp, own, blk, s1 - s0 - 1u, x);
-          o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
+    // all sub-steps of this tile; WC >= 0: uniform-width stream of WC terms per row (no offset table, straight-line body)
+    auto substeps = [&](auto wc) {
+      constexpr int WC = decltype(wc)::value;
+      for (uint32_t step = 0; step < p.niter; ++step) {
+        for (uint32_t b = warp; b < nblocks; b += nwarps) {
+          const uint32_t row = b * R + rr;
+          const int4 own = lds128i(lp + row * (TW * 4u));
+          int4 o = make_int4(0, 0, 0, 0);
+          if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
+            uint32_t s0, W = 0;
+            if constexpr (WC >= 0) s0 = b * (uint32_t)(WC + 1);
+            else { s0 = s_boff[b]; W = s_boff[b + 1] - s0 - 1u; }
+            RecCol<TW, BSMEM> blk;
+            blk.a = strm_s + s0 * (R * 16u);
+            blk.p = strm + (size_t)s0 * R + rr;
+            double x[4];
+            gen_x<TW, BSMEM, WC>(lp, own, blk, W, x);
+            o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
+          }
+          asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
         }
-        asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+        __syncthreads();
+        int32_t* tmp = src; src = dst; dst = tmp;
+        const uint32_t tl = lp; lp = lq; lq = tl;
       }
-      __syncthreads();
-      int32_t* tmp = src; src = dst; dst = tmp;
-      const uint32_t tl = lp; lp = lq; lq = tl;
-    }
+    };
+#ifndef ECO_GEN_MULTI_NOWC
+    if (p.uslots == 4u) substeps(std::integral_constant<int, 3>{});        // the scripts' random_interaction(3,0)
+    else if (p.uslots == 3u) substeps(std::integral_constant<int, 2>{});
+    else
+#endif
+      substeps(std::integral_constant<int, -1>{});
     const int4* s4 = reinterpret_cast<const int4*>(src);
     int4* g4 = reinterpret_cast<int4*>(gt);
     for (uint32_t i = threadIdx.x; i < tile_words / 4; i += THREADS) g4[i] = s4[i];
