@@ -185,7 +185,9 @@ __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSME
 // `lp` = shared address of the tile + 16*quad; `own` = the lane's own densities; `blk` = this lane's record column
 // of the block (header first); W = terms per row (warp-uniform, the same for all NS blocks).
 // WC >= 0: the width is the compile-time constant WC (<= 4) and W is ignored -- no width dispatch per warp-op.
-template <int TW, bool BSMEM, int NS, int WC = -1>
+// PIPE: rows of 8+ terms go through gen_terms_pipelined (only where the register budget allows: the 25-warp pipeline kernel;
+// in the 1024-thread multi-step kernel its 12 extra vector registers cost the short rows 14 %).
+template <int TW, bool BSMEM, int NS, int WC = -1, bool PIPE = false>
 __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], const RecCol<TW, BSMEM> (&blk)[NS], uint32_t W,
                                         double (&x)[NS][4]) {
   double d[NS][4], ir[NS][4], rr[NS];
@@ -203,7 +205,7 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
   }
   if constexpr (WC > 0) gen_terms<TW, BSMEM, NS, WC>(lp, e, ir);
   if constexpr (WC >= 0) W = 0;
-  if constexpr (NS == 1) {
+  if constexpr (NS == 1 && PIPE) {
     if (W >= 8) gen_terms_pipelined<TW, BSMEM, NS>(lp, e, W, ir);   // leaves W < 4
   }
   for (; W >= 4; W -= 4) {
@@ -223,12 +225,12 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     for (int k = 0; k < 4; ++k) x[s][k] = __dadd_rn(d[s][k], __dmul_rn(d[s][k], __dadd_rn(rr[s], ir[s][k])));
 }
 
-template <int TW, bool BSMEM, int WC = -1>
+template <int TW, bool BSMEM, int WC = -1, bool PIPE = false>
 __device__ __forceinline__ void gen_x(uint32_t lp, const int4 own, const RecCol<TW, BSMEM>& blk, uint32_t W, double x[4]) {
   const int4 o1[1] = {own};
   const RecCol<TW, BSMEM> b1[1] = {blk};
   double x1[1][4];
-  gen_x_n<TW, BSMEM, 1, WC>(lp, o1, b1, W, x1);
+  gen_x_n<TW, BSMEM, 1, WC, PIPE>(lp, o1, b1, W, x1);
   x[0] = x1[0][0]; x[1] = x1[0][1]; x[2] = x1[0][2]; x[3] = x1[0][3];
 }
 
@@ -372,7 +374,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
           RecCol<TW, BSMEM> blk;
           blk.a = strm_s + b * blk_bytes; blk.p = p.stream + (size_t)b * uslots * R + rr;
           double x[4];
-          gen_x<TW, BSMEM>(lp, own, blk, W, x);
+          gen_x<TW, BSMEM, -1, true>(lp, own, blk, W, x);
           const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
           __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
         }
@@ -417,11 +419,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       blk.p = p.stream + (size_t)s0 * R + rr;
       double x[4];
 #ifndef ECO_ABLATE
-      gen_x<TW, BSMEM>(lp, own, blk, W, x);
+      gen_x<TW, BSMEM, -1, true>(lp, own, blk, W, x);
       const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
       __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
 #else   // cost-attribution builds (tools/ablate.sh): results are wrong on purpose, never shipped
-      gen_x<TW, BSMEM>(lp, own, blk, (ECO_ABLATE & 2) ? 0u : W, x);
+      gen_x<TW, BSMEM, -1, true>(lp, own, blk, (ECO_ABLATE & 2) ? 0u : W, x);
       const uint4 u = (ECO_ABLATE & 1) ? make_uint4(row, row * 3u, xq, yg) : philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk);
       int4 o;
       if (ECO_ABLATE & 4) o = make_int4(__double2loint(x[0]) ^ u.x, __double2loint(x[1]) ^ u.y, __double2loint(x[2]) ^ u.z, __double2loint(x[3]) ^ u.w);
@@ -441,7 +443,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
 // generate(niter > 1): per tile, `niter` Jacobi steps between two shared-memory buffers (HBM traffic amortised
 // over niter -- the scripts' cadence is generate(100), models/spatial_ecolab.py:67), CTA-wide barrier per step.
 // ---------------------------------------------------------------------------------------------------------
-template <int TW, int THREADS, bool BSMEM>
+// WC >= 0: uniform-width stream of WC terms per row (p.uslots == WC + 1): no offset table, one straight-line term body.
+template <int TW, int THREADS, bool BSMEM, int WC = -1>
 __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -482,38 +485,28 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
     int32_t* src = buf0;
     int32_t* dst = buf1;
     uint32_t lp = buf0_s, lq = buf0_s + tile_bytes;   // shared addresses of src / dst (+ 16*quad)
-    // all sub-steps of this tile; WC >= 0: uniform-width stream of WC terms per row (no offset table, straight-line body)
-    auto substeps = [&](auto wc) {
-      constexpr int WC = decltype(wc)::value;
-      for (uint32_t step = 0; step < p.niter; ++step) {
-        for (uint32_t b = warp; b < nblocks; b += nwarps) {
-          const uint32_t row = b * R + rr;
-          const int4 own = lds128i(lp + row * (TW * 4u));
-          int4 o = make_int4(0, 0, 0, 0);
-          if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
-            uint32_t s0, W = 0;
-            if constexpr (WC >= 0) s0 = b * (uint32_t)(WC + 1);
-            else { s0 = s_boff[b]; W = s_boff[b + 1] - s0 - 1u; }
-            RecCol<TW, BSMEM> blk;
-            blk.a = strm_s + s0 * (R * 16u);
-            blk.p = strm + (size_t)s0 * R + rr;
-            double x[4];
-            gen_x<TW, BSMEM, WC>(lp, own, blk, W, x);
-            o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
-          }
-          asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+    for (uint32_t step = 0; step < p.niter; ++step) {
+      for (uint32_t b = warp; b < nblocks; b += nwarps) {
+        const uint32_t row = b * R + rr;
+        const int4 own = lds128i(lp + row * (TW * 4u));
+        int4 o = make_int4(0, 0, 0, 0);
+        if (__any_sync(FULL, (own.x | own.y | own.z | own.w) != 0)) {
+          uint32_t s0, W = 0;
+          if constexpr (WC >= 0) s0 = b * (uint32_t)(WC + 1);
+          else { s0 = s_boff[b]; W = s_boff[b + 1] - s0 - 1u; }
+          RecCol<TW, BSMEM> blk;
+          blk.a = strm_s + s0 * (R * 16u);
+          blk.p = strm + (size_t)s0 * R + rr;
+          double x[4];
+          gen_x<TW, BSMEM, WC>(lp, own, blk, W, x);
+          o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
         }
-        __syncthreads();
-        int32_t* tmp = src; src = dst; dst = tmp;
-        const uint32_t tl = lp; lp = lq; lq = tl;
+        asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
       }
-    };
-#ifndef ECO_GEN_MULTI_NOWC
-    if (p.uslots == 4u) substeps(std::integral_constant<int, 3>{});        // the scripts' random_interaction(3,0)
-    else if (p.uslots == 3u) substeps(std::integral_constant<int, 2>{});
-    else
-#endif
-      substeps(std::integral_constant<int, -1>{});
+      __syncthreads();
+      int32_t* tmp = src; src = dst; dst = tmp;
+      const uint32_t tl = lp; lp = lq; lq = tl;
+    }
     const int4* s4 = reinterpret_cast<const int4*>(src);
     int4* g4 = reinterpret_cast<int4*>(gt);
     for (uint32_t i = threadIdx.x; i < tile_words / 4; i += THREADS) g4[i] = s4[i];
