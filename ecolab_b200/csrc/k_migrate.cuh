@@ -32,7 +32,7 @@
 #define ECO_MIG_THREADS 256
 #endif
 #ifndef ECO_MIG_PF
-#define ECO_MIG_PF 0      // grid rows between an L2 prefetch and the register load of a row; 0 = none (measured: 4/8/16 rows ahead all SLOWER, 2.3-2.6 vs 1.85 ms on C3)
+#define ECO_MIG_PF 0      // grid rows between an L2 prefetch and the register load of a row; 0 = none (per-lane prefetches in the earlier kernel: 4/8/16 rows ahead all SLOWER, 2.3-2.6 vs 1.85 ms on C3); now counted in trips of ECO_MIG_NB rows, bulk prefetch per warp row
 #endif
 
 namespace eco {
@@ -184,7 +184,18 @@ __device__ __forceinline__ void mig_unit(const int32_t* __restrict__ p0, const i
                    flux(c, big(up.w), k.b[3]));                                             // T(n[y-1] - n[y])
   uint32_t i = 0;
   const int32_t* pl = p0 + (long long)(NB + 1) * stride;                                    // row(i+NB+1)
+#if ECO_MIG_PF > 0   // experiment (warp span T = 1 only): the warp's 512-byte rows requested into L2 ECO_MIG_PF trips ahead, one bulk prefetch per row
+  const uint32_t pf_lane = threadIdx.x & 31u;
+  const int32_t* wb = p0 - 4 * pf_lane;
+  if (pf_lane < ECO_MIG_PF * NB && NB + 1 + pf_lane < n) bulk_prefetch_l2(wb + (long long)(NB + 1 + pf_lane) * stride, 512u);
+#endif
   for (; i + 2 * NB < n; i += NB) {                                                         // NB rows per trip, no register rotation
+#if ECO_MIG_PF > 0
+    if (pf_lane < NB) {
+      const uint32_t pr = i + NB + 1 + ECO_MIG_PF * NB + pf_lane;
+      if (pr < n) bulk_prefetch_l2(wb + (long long)pr * stride, 512u);
+    }
+#endif
 #pragma unroll
     for (int j = 0; j < NB; ++j) {
       const MigNext nx = mig_unpack(r[j]);
