@@ -173,8 +173,8 @@ def build_model(E, args, nx, ny, comm, device, stream):
             getattr(m, k)(v)
     m.setGrid(nx, ny)
     m.seed(10)
-    for knob, val in (("gen_threads", args.gen_warps), ("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem),
-                      ("mig_variant", args.mig_variant), ("gen_dual", args.gen_dual)):
+    for knob, val in (("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem), ("mig_variant", args.mig_variant),
+                      ("mig_stages", args.mig_stages), ("gen_dual", args.gen_dual)):
         if val:
             m.set_tuning(knob, val)
     m.fill_density_random(0, 199)   # mean 100, with gradients between neighbours so migrate really moves population
@@ -358,6 +358,7 @@ def run_dense(args):
     m.mutation(np.full(nsp, 1e-5)); m.migration(np.full(nsp, 0.1)); m.create(np.zeros(nsp))
     m.setGrid(nx, ny)
     m.seed(10)
+    m.set_tuning("gen_dense", 1)        # the tensor path is opt-in (not bit-exact against the FP64 summation order)
     if args.dense_slices:
         m.set_tuning("dense_slices", args.dense_slices)
     m.fill_density_random(0, args.dense_dmax)   # < 256: one u8 slice per density; larger: two
@@ -432,7 +433,7 @@ def main():
     ap.add_argument("--nsp", type=int, default=1024)
     ap.add_argument("--nnz", type=int, default=3)
     ap.add_argument("--e2e-n", type=int, default=1024, dest="e2e_n")
-    ap.add_argument("--gen-warps", type=int, default=0, dest="gen_warps")
+    ap.add_argument("--mig-stages", type=int, default=0, dest="mig_stages")
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
     ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
     ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")

@@ -45,6 +45,8 @@ SIGNATURES = {
     "eco_get_density": [_vp, _sz, _vp, _sz, _P(_sz)],
     "eco_set_density_all": [_vp, _vp, _sz, _sz],
     "eco_get_density_all": [_vp, _vp, _sz, _sz],
+    "eco_get_density_rows": [_vp, _sz, _sz, _vp, _sz],
+    "eco_set_density_rows": [_vp, _sz, _sz, _vp, _sz],
     "eco_set_density_all_device": [_vp, _vp, _sz, _sz],
     "eco_get_density_all_device": [_vp, _vp, _sz, _sz],
     "eco_fill_density": [_vp, _i32],
@@ -55,6 +57,8 @@ SIGNATURES = {
     "eco_generate": [_vp, C.c_uint],
     "eco_migrate": [_vp, _P(_u64)],
     "eco_step": [_vp, C.c_uint, _P(_u64)],
+    "eco_step_async": [_vp, C.c_uint],
+    "eco_migrate_wait": [_vp, _P(_u64)],
     "eco_step_host": [_vp, _vp, _vp, _sz, _sz, C.c_uint, _P(_u64)],
     "eco_condense": [_vp, _P(C.c_uint)],
     "eco_mutate": [_vp],
@@ -70,9 +74,9 @@ SIGNATURES = {
     "eco_migrate_local": [_vp, _P(_u64)],
     "eco_migrate_local_async": [_vp, _P(_vp)],
     "eco_halo_ptrs": [_vp, _P(_vp), _P(_vp), _P(_vp), _P(_vp), _P(_sz)],
-    "eco_ipc_export": [_vp, _vp, _P(_sz), _P(_sz)],
-    "eco_ipc_import": [_vp, _vp, _P(_vp)],
-    "eco_set_peer_rows": [_vp, _vp, _vp],
+    "eco_peer_export": [_vp, _vp, _sz],
+    "eco_peer_connect": [_vp, _vp, _vp],
+    "eco_peer_disconnect": [_vp],
     "eco_alive_mask": [_vp, _vp, _sz],
     "eco_condense_apply": [_vp, _vp, _sz, _P(C.c_uint)],
     "eco_mutate_cells": [_vp, _P(_sz)],

@@ -66,6 +66,9 @@ Engine::Engine(int device) : device_(device) {
   CK(cudaMalloc(&d_total_, 4 * sizeof(unsigned long long)));
   CK(cudaMemset(d_total_, 0, 4 * sizeof(unsigned long long)));
   CK(cudaMallocHost(&h_total_, 4 * sizeof(unsigned long long)));
+  memset(h_total_, 0, 4 * sizeof(unsigned long long));
+  CK(cudaMalloc(&d_flags_, 4 * sizeof(unsigned int)));
+  CK(cudaMemset(d_flags_, 0, 4 * sizeof(unsigned int)));
   cudaEvent_t ev;
   CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   ev_total_ = ev;
@@ -74,7 +77,9 @@ Engine::Engine(int device) : device_(device) {
 Engine::~Engine() {
   cudaSetDevice(device_);
   cudaDeviceSynchronize();
+  try { peer_disconnect(); } catch (...) {}
   free_buffers();
+  cudaFree(d_flags_);
   cudaFree(d_boff_); cudaFree(d_stream_);
   cudaFree(d_aop_); cudaFree(d_bop_); cudaFree(d_dsp_); cudaFree(d_partial_); cudaFree(d_maxn_); cudaFree(dense_prof_);
   if (h_maxn_) cudaFreeHost(h_maxn_);
@@ -104,6 +109,8 @@ void Engine::sync() {
 }
 
 void Engine::free_buffers() {
+  peer_disconnect();   // the neighbours' row pointers were computed for the old geometry
+  ++buf_version_;
   for (int i = 0; i < 2; ++i) {
     if (buf_[i]) cudaFree(buf_[i]);
     buf_[i] = nullptr;
@@ -145,6 +152,7 @@ void Engine::ensure_other() {
   const size_t bytes = (size_t)(ny_ + 2) * row_stride() * sizeof(int32_t);
   CK(cudaMalloc(&buf_[cur_ ^ 1], bytes));
   CK(cudaMemsetAsync(buf_[cur_ ^ 1], 0, bytes, ST));
+  ++buf_version_;
 }
 
 void Engine::set_grid(uint32_t nx, uint32_t ny_global, uint32_t y0, uint32_t ny, uint32_t nsp) {
@@ -152,7 +160,6 @@ void Engine::set_grid(uint32_t nx, uint32_t ny_global, uint32_t y0, uint32_t ny,
   sync();
   nx_ = nx; nyg_ = ny_global; y0_ = y0; ny_ = ny;
   nsp_ = nsp;
-  peer_top_ = peer_bottom_ = nullptr;
   alloc_buffers(round_up32(nsp));
 }
 
@@ -172,6 +179,8 @@ void Engine::resize_species(uint32_t nsp) {
   // grow: new capacity with head-room (and possibly a narrower tile), re-layout into a fresh buffer
   const uint32_t new_cap = round_up32(nsp + nsp / 4 + 16);
   const uint32_t new_tw = pick_tile_width(new_cap);
+  peer_disconnect();
+  ++buf_version_;
   int32_t* old_cur = buf_[cur_];
   int32_t* old_other = buf_[cur_ ^ 1];
   CK(cudaStreamSynchronize(ST));
@@ -196,7 +205,6 @@ void Engine::resize_species(uint32_t nsp) {
   buf_[0] = nb;
   cur_ = 0;
   nsp_ = nsp;
-  peer_top_ = peer_bottom_ = nullptr;
 }
 
 // ===========================================================================================
@@ -268,6 +276,46 @@ void Engine::get_density_all(int32_t* host, size_t nsp) {
   }
   get_density_all_dev(d_stage_, nsp);
   CK(cudaMemcpyAsync(host, d_stage_, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ST));
+  CK(cudaStreamSynchronize(ST));
+}
+
+void Engine::get_density_rows(uint32_t r0, uint32_t nrows, int32_t* host, size_t nsp) {
+  CK(cudaSetDevice(device_));
+  if (nsp != nsp_) throw std::runtime_error("get_density_rows: species count mismatch");
+  if ((uint64_t)r0 + nrows > ny_) throw std::runtime_error("get_density_rows: rows outside the owned slab");
+  const size_t n = (size_t)nx_ * nrows * nsp;
+  if (!n) return;
+  if (n > stage_cap_) {
+    if (d_stage_) CK(cudaFree(d_stage_));
+    CK(cudaMalloc(&d_stage_, n * sizeof(int32_t)));
+    stage_cap_ = n;
+  }
+  const unsigned long long nwork = (unsigned long long)((nx_ + 31) / 32) * nrows * ((nsp_ + 31) / 32);
+  transpose_kernel<false><<<(unsigned)std::min<unsigned long long>(nwork, 148ull * 64), 1024, 0, ST>>>(
+      make_layout(row0(cur_) + (size_t)r0 * row_stride(), tw_, cap_, ntx_, nx_, nrows, y0_ + r0, nyg_, nsp_), d_stage_);
+  CK(cudaGetLastError());
+  ++launches_;
+  CK(cudaMemcpyAsync(host, d_stage_, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ST));
+  CK(cudaStreamSynchronize(ST));
+}
+
+void Engine::set_density_rows(uint32_t r0, uint32_t nrows, const int32_t* host, size_t nsp) {
+  CK(cudaSetDevice(device_));
+  if (nsp != nsp_) throw std::runtime_error("set_density_rows: species count mismatch");
+  if ((uint64_t)r0 + nrows > ny_) throw std::runtime_error("set_density_rows: rows outside the owned slab");
+  const size_t n = (size_t)nx_ * nrows * nsp;
+  if (!n) return;
+  if (n > stage_cap_) {
+    if (d_stage_) CK(cudaFree(d_stage_));
+    CK(cudaMalloc(&d_stage_, n * sizeof(int32_t)));
+    stage_cap_ = n;
+  }
+  CK(cudaMemcpyAsync(d_stage_, host, n * sizeof(int32_t), cudaMemcpyHostToDevice, ST));
+  const unsigned long long nwork = (unsigned long long)((nx_ + 31) / 32) * nrows * ((nsp_ + 31) / 32);
+  transpose_kernel<true><<<(unsigned)std::min<unsigned long long>(nwork, 148ull * 64), 1024, 0, ST>>>(
+      make_layout(row0(cur_) + (size_t)r0 * row_stride(), tw_, cap_, ntx_, nx_, nrows, y0_ + r0, nyg_, nsp_), d_stage_);
+  CK(cudaGetLastError());
+  ++launches_;
   CK(cudaStreamSynchronize(ST));
 }
 

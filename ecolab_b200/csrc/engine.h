@@ -56,6 +56,9 @@ class Engine {
   // device staging buffer and a transposing kernel
   void set_density_all(const int32_t* host, size_t nsp);
   void get_density_all(int32_t* host, size_t nsp);
+  // owned grid rows [r0, r0+nrows) (LOCAL row index), host buffer cell-major [cell][nsp]
+  void get_density_rows(uint32_t r0, uint32_t nrows, int32_t* host, size_t nsp);
+  void set_density_rows(uint32_t r0, uint32_t nrows, const int32_t* host, size_t nsp);
   // same with a DEVICE cell-major buffer (used by bench to build big states)
   void set_density_all_dev(const int32_t* dev, size_t nsp);
   void get_density_all_dev(int32_t* dev, size_t nsp);
@@ -94,11 +97,22 @@ class Engine {
   void halo_ptrs(void** send_top, void** send_bottom, void** recv_top, void** recv_bottom);
   size_t row_bytes() const { return (size_t)ntx_ * cap_ * tw_ * sizeof(int32_t); }
   uint32_t tile_width() const { return tw_; }
-  // Optional peer pointers (CUDA IPC / P2P): when set, migrate reads the
-  // neighbour slabs' boundary rows directly over NVLink instead of ghost rows.
-  void set_peer_rows(const void* top_peer_row, const void* bottom_peer_row);
-  int ipc_export(void* handle_out64, size_t* offset_top, size_t* offset_bottom);
-  void* ipc_import(const void* handle64);
+  // Halo over peer memory (CUDA IPC, NVLink): once connected, migrate's boundary units copy the neighbour slabs'
+  // boundary rows straight out of the neighbours' buffers -- no ghost-row exchange, no collective.  Ordering is a
+  // device-side epoch counter per rank: migrate() first publishes "everything before this migrate is done" (epoch e),
+  // and a boundary unit waits until the neighbour's counter has reached e before it touches the neighbour's row.
+  // The neighbour's counter reaching e also means its migrate e-1 has finished reading OUR rows, which is what makes
+  // overwriting the destination buffer safe.  Every rank must call migrate the same number of times.
+  struct PeerBlob {
+    unsigned char handle[3][64];   // cudaIpcMemHandle_t of buffer 0, buffer 1, the flag words
+    uint32_t ny, cap, tw, ntx;     // geometry of the exporting slab (its last owned row depends on ny)
+    uint64_t version;
+  };
+  void peer_export(PeerBlob* out);                                  // allocates the second buffer if needed
+  void peer_connect(const PeerBlob* top, const PeerBlob* bottom);   // neighbour above (lower y) / below; nullptr = none
+  void peer_disconnect();
+  bool peer_connected() const { return peer_open_[0] || peer_open_[1]; }
+  uint64_t buf_version() const { return buf_version_; }            // bumped whenever a density buffer is (re)allocated
 
   // x = n + n*(r+ir) before ROUND for one generate sub-step, cell-major [cell][nsp]; densities untouched
   void pre_rounding(double* out_host);
@@ -117,15 +131,14 @@ class Engine {
   void last_kernel_config(int* grid, int* block, int* smem) const {
     *grid = last_grid_; *block = last_block_; *smem = last_smem_;
   }
-  // tuning knobs (bench/profiling): 0 = auto.  gen_variant: consumer warps of the generate pipeline (12/16/20 with two
-  // blocks per warp, 24/31 with one); gen_stages: shared-memory tile buffers; mig_variant: tiles a migrate warp spans
-  int gen_variant = 0;
+  // tuning knobs (bench/profiling): 0 = auto.  gen_stages: shared-memory tile buffers of the generate pipeline
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory
-  int gen_dual = 0;      // generate(1): two species-row blocks per consumer warp at a time; 0 = auto, 1 = on, -1 = off
-  int mig_variant = 0;
-  // dense (tensor-core) generate, k_dense.cuh.  gen_dense: 0 = automatic (beta at least half full and >= 128 species),
-  // 1 = always, -1 = never.  dense_slices = P, the 8-bit slices beta is cut into (3: 2^-24 of the row maximum; 7: FP64).
+  int gen_dual = 0;      // generate(1): two species-row blocks per consumer warp at a time; 0 / 1 = where applicable, -1 = off
+  int mig_variant = 0;   // 0 = automatic (tile-column pipeline where the tile width allows), 1 = register walker, 2 = pipeline
+  int mig_stages = 0;    // ring depth of the migrate pipeline; 0 = default
+  // dense (tensor-core) generate, k_dense.cuh.  gen_dense: 1 = use it, 0 / -1 = never (default: it is not bit-exact against
+  // the reference's FP64 summation order, so the caller must ask for it).  dense_slices = P, the 8-bit slices beta is cut into (3: 2^-24 of the row maximum; 7: FP64).
   int gen_dense = 0;
   int dense_slices = 3;
   bool dense_wanted() const;
@@ -158,13 +171,20 @@ class Engine {
   uint32_t nsp_ = 0, cap_ = 0, tw_ = 32;   // live species rows, allocated rows, tile width (cells)
   int32_t* buf_[2] = {nullptr, nullptr};   // allocations (with ghost rows)
   int cur_ = 0;
-  const void* peer_top_ = nullptr;
-  const void* peer_bottom_ = nullptr;
+  // peer halo: [buffer index][side: 0 = above, 1 = below] boundary-row pointers inside the neighbours' buffers
+  const void* peer_[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  const unsigned int* peer_flag_[2] = {nullptr, nullptr};
+  void* peer_map_[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // opened IPC mappings per side
+  bool peer_open_[2] = {false, false};
+  unsigned int* d_flags_ = nullptr;      // [0] epoch published by this rank, [2] error word; IPC-exported
+  unsigned int gen_epoch_ = 0;
+  uint64_t buf_version_ = 0;
 
   // beta on device
   uint32_t nblocks_ = 0, beta_tw_ = 0, beta_nsp_ = 0;   // ELL blocks; the tile width / species count it was built for
   uint32_t* d_boff_ = nullptr; void* d_stream_ = nullptr;   // blocked-ELL stream (k_generate.cuh)
   size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_slots_ = 0;
+  bool beta_fma_ok_ = true;    // every beta entry is zero or a normal number below 2^971: the exact-FMA product applies
   uint32_t beta_uslots_ = 0;   // != 0: every block of the stream has this many slots (uniform width, no offset table reads)
   BetaCsr beta_host_;                                   // kept to re-block when the tile width changes
 

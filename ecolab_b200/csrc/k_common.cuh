@@ -83,22 +83,11 @@ __device__ __forceinline__ int round_stoch(double x, uint32_t u) {
 
 // the same for 0 <= x < 2^31-256 (callers check the range on x's high word): both clamps are no-ops there.
 // x = +0 gives trunc 0, frac 0, ceil(0) = 0 > u false -> 0, as the reference's x<=0 branch.
-#ifndef ECO_ROUND_VARIANT
-#define ECO_ROUND_VARIANT 0
-#endif
 __device__ __forceinline__ int round_stoch_inrange(double x, uint32_t u) {
   const double t = __dadd_rz(x, TWO52);
-#if ECO_ROUND_VARIANT & 2   // trunc(x) back to double on the conversion pipe instead of a second FP64 add
-  const double f = __dadd_rn(x, -(double)__double2loint(t));
-#else
   const double f = __dadd_rn(x, -__dadd_rn(t, -TWO52));
-#endif
   const uint32_t cp = (uint32_t)__double2loint(__dadd_ru(__dmul_rn(f, 4294967295.0), TWO52));
-#if ECO_ROUND_VARIANT & 1   // cp > u as the borrow of u - cp: two integer instructions instead of add/compare/select
-  return __double2loint(t) + (int)(((unsigned long long)u - (unsigned long long)cp) >> 63);
-#else
   return __double2loint(t) + (cp > u ? 1 : 0);
-#endif
 }
 
 // ---- mbarrier / bulk-copy (TMA unit) wrappers ------------------------------------------------

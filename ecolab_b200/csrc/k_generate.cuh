@@ -5,8 +5,14 @@
 // ROWS = 128/TW at a time (one warp-op: ROWS rows x TW cells, a lane owns 4 consecutive cells of one row).
 // Block b occupies the 16-byte records  stream[boff[b]*ROWS ... boff[b+1]*ROWS):
 //     slot 0      : ROWS headers  { double diag ; double repro_rate }
-//     slot 1..W_b : ROWS terms    { double val ; uint32 byte offset of species row `col` inside a tile ; pad }
+//     slot 1..W_b : ROWS terms    { double val ; uint32 byte offset of species row `col` inside a tile ;
+//                                   uint32 high word of c = -(val * 2^52) }
 // where W_b = longest row of the block (shorter rows are padded with val = 0, offset 0).
+// The fourth word turns the product val*n into ONE instruction with no int -> double conversion: with B = 2^52 + n (the
+// density paired with a constant high word) fma(val, B, c) = fl(val*B - val*2^52) = fl(val*n) -- the fused multiply-add
+// forms val*B exactly and rounds once, so the result is bit-identical to the reference's separately rounded product
+// val*(double)n (models/ecolab_model.cc:100).  c shares val's low word (scaling by 2^52 keeps the mantissa) as long as val
+// is zero or a normal number below 2^971; the host checks that and otherwise selects the FMA = false instantiation.
 // A warp-op therefore reads its whole beta block through ONE base pointer with immediate offsets.
 // Terms of a row keep the COO order (reference oDiagIdx, :718-723) so the FP64 summation order is the reference's:
 //     ir = diag*n ; ir = ir + val_j*n[col_j] (j ascending) ; x = n + n*(r + ir), every operation individually rounded.
@@ -63,12 +69,9 @@ struct RecCol {
 };
 
 // Philox4x32-10 with the key schedule taken from kernel parameters (constant bank operands, no key arithmetic)
-#ifndef ECO_PHILOX_ROUNDS
-#define ECO_PHILOX_ROUNDS 10   // the RNG contract (k_common.cuh, oracle); other values exist only to price the contract
-#endif
 __device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t (&rk)[20]) {
 #pragma unroll
-  for (int r = 0; r < ECO_PHILOX_ROUNDS; ++r) {
+  for (int r = 0; r < 10; ++r) {
     const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
     const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
     const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk[2 * r];
@@ -82,14 +85,8 @@ __device__ __forceinline__ double dbl(uint32_t lo, uint32_t hi) { return __hiloi
 
 // int -> double of a density.  Two exact routes: I2F on the conversion (XU) pipe -- one issue slot, 8 pipe cycles per
 // warp on a quarter-rate unit -- or (2^52+n) - 2^52 on the FP64 pipe -- three issue slots (pair build + DADD), 2 pipe
-// cycles.  ECO_GEN_CVT_G: gathered densities of term j go through FP64 when bit (j & 1) of the mask is set (0 = all XU,
-// 3 = all FP64, 2 = odd terms only); ECO_GEN_CVT_OWN likewise for the lane's own densities.
-#ifndef ECO_GEN_CVT_G
-#define ECO_GEN_CVT_G 2      // measured on C3, 3 terms: 0 -> 2.20 ms, 2 -> 2.14, 3 -> 2.15; own densities through FP64: no gain
-#endif
-#ifndef ECO_GEN_CVT_OWN
-#define ECO_GEN_CVT_OWN 0
-#endif
+// cycles.  Only the FMA = false path converts gathered densities: odd terms through FP64, even terms through XU
+// (measured on C3, 3 terms: all XU 2.20 ms, odd FP64 2.14, all FP64 2.15).
 template <bool FP64PIPE>
 __device__ __forceinline__ double cvt_n(int n) {
   if (FP64PIPE) return u2d((uint32_t)n);
@@ -115,14 +112,20 @@ __device__ __forceinline__ void gen_gather(uint32_t lp, const uint4 (&w)[NS][NT]
 #pragma unroll
     for (int j = 0; j < NT; ++j) g[s][j] = lds128i(lp + w[s][j].z);
 }
-template <int NS, int NT>
+template <int NS, int NT, bool FMA>
 __device__ __forceinline__ void gen_accumulate(const uint4 (&w)[NS][NT], const int4 (&g)[NS][NT], double (&ir)[NS][4]) {
 #pragma unroll
   for (int j = 0; j < NT; ++j)
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
       const double v = dbl(w[s][j].x, w[s][j].y);
-      if ((ECO_GEN_CVT_G >> (j & 1)) & 1) {
+      if (FMA) {
+        const double c = dbl(w[s][j].x, w[s][j].w);   // -(v * 2^52)
+        ir[s][0] = __dadd_rn(ir[s][0], __fma_rn(v, __hiloint2double(0x43300000, g[s][j].x), c));
+        ir[s][1] = __dadd_rn(ir[s][1], __fma_rn(v, __hiloint2double(0x43300000, g[s][j].y), c));
+        ir[s][2] = __dadd_rn(ir[s][2], __fma_rn(v, __hiloint2double(0x43300000, g[s][j].z), c));
+        ir[s][3] = __dadd_rn(ir[s][3], __fma_rn(v, __hiloint2double(0x43300000, g[s][j].w), c));
+      } else if (j & 1) {
         ir[s][0] = __dadd_rn(ir[s][0], __dmul_rn(v, cvt_n<true>(g[s][j].x)));
         ir[s][1] = __dadd_rn(ir[s][1], __dmul_rn(v, cvt_n<true>(g[s][j].y)));
         ir[s][2] = __dadd_rn(ir[s][2], __dmul_rn(v, cvt_n<true>(g[s][j].z)));
@@ -135,19 +138,19 @@ __device__ __forceinline__ void gen_accumulate(const uint4 (&w)[NS][NT], const i
       }
     }
 }
-template <int TW, bool BSMEM, int NS, int NT>
+template <int TW, bool BSMEM, int NS, int NT, bool FMA>
 __device__ __forceinline__ void gen_terms(uint32_t lp, const RecCol<TW, BSMEM> (&e)[NS], double (&ir)[NS][4]) {
   uint4 w[NS][NT];
   int4 g[NS][NT];
   gen_load_recs<TW, BSMEM, NS, NT>(e, 0, w);
   gen_gather<NS, NT>(lp, w, g);
-  gen_accumulate<NS, NT>(w, g, ir);
+  gen_accumulate<NS, NT, FMA>(w, g, ir);
 }
 
 // Long rows (W >= 8), four terms at a time: the records of the NEXT four terms are requested before the arithmetic of
 // the current four, so their latency (L2 when the stream does not fit in shared memory: ~300 cycles, it was the top
 // stall of the 51-term profile) hides behind ~60 FP64 operations.  Two record buffers alternate: no register copies.
-template <int TW, bool BSMEM, int NS>
+template <int TW, bool BSMEM, int NS, bool FMA>
 __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSMEM> (&e)[NS], uint32_t& W, double (&ir)[NS][4]) {
   uint4 wa[NS][4], wb[NS][4];
   int4 g[NS][4];
@@ -155,10 +158,10 @@ __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSME
   while (W >= 12) {                       // wa holds terms [0,4) of e; at least 8 more follow
     gen_gather<NS, 4>(lp, wa, g);
     gen_load_recs<TW, BSMEM, NS, 4>(e, 4, wb);
-    gen_accumulate<NS, 4>(wa, g, ir);
+    gen_accumulate<NS, 4, FMA>(wa, g, ir);
     gen_gather<NS, 4>(lp, wb, g);
     gen_load_recs<TW, BSMEM, NS, 4>(e, 8, wa);
-    gen_accumulate<NS, 4>(wb, g, ir);
+    gen_accumulate<NS, 4, FMA>(wb, g, ir);
 #pragma unroll
     for (int s = 0; s < NS; ++s) e[s] = e[s].advance(8);
     W -= 8;
@@ -167,14 +170,14 @@ __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSME
   gen_gather<NS, 4>(lp, wa, g);
   if (W >= 8) {
     gen_load_recs<TW, BSMEM, NS, 4>(e, 4, wb);
-    gen_accumulate<NS, 4>(wa, g, ir);
+    gen_accumulate<NS, 4, FMA>(wa, g, ir);
     gen_gather<NS, 4>(lp, wb, g);
-    gen_accumulate<NS, 4>(wb, g, ir);
+    gen_accumulate<NS, 4, FMA>(wb, g, ir);
 #pragma unroll
     for (int s = 0; s < NS; ++s) e[s] = e[s].advance(8);
     W -= 8;
   } else {
-    gen_accumulate<NS, 4>(wa, g, ir);
+    gen_accumulate<NS, 4, FMA>(wa, g, ir);
 #pragma unroll
     for (int s = 0; s < NS; ++s) e[s] = e[s].advance(4);
     W -= 4;
@@ -187,7 +190,7 @@ __device__ __forceinline__ void gen_terms_pipelined(uint32_t lp, RecCol<TW, BSME
 // WC >= 0: the width is the compile-time constant WC (<= 4) and W is ignored -- no width dispatch per warp-op.
 // PIPE: rows of 8+ terms go through gen_terms_pipelined (only where the register budget allows: the 25-warp pipeline kernel;
 // in the 1024-thread multi-step kernel its 12 extra vector registers cost the short rows 14 %).
-template <int TW, bool BSMEM, int NS, int WC = -1, bool PIPE = false>
+template <int TW, bool BSMEM, int NS, int WC = -1, bool PIPE = false, bool FMA = true>
 __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], const RecCol<TW, BSMEM> (&blk)[NS], uint32_t W,
                                         double (&x)[NS][4]) {
   double d[NS][4], ir[NS][4], rr[NS];
@@ -197,26 +200,26 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     const uint4 h = blk[s].ld(0);
     const double diag = dbl(h.x, h.y);
     rr[s] = dbl(h.z, h.w);
-    d[s][0] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].x); d[s][1] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].y);
-    d[s][2] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].z); d[s][3] = cvt_n<ECO_GEN_CVT_OWN != 0>(own[s].w);
+    d[s][0] = cvt_n<false>(own[s].x); d[s][1] = cvt_n<false>(own[s].y);
+    d[s][2] = cvt_n<false>(own[s].z); d[s][3] = cvt_n<false>(own[s].w);
 #pragma unroll
     for (int k = 0; k < 4; ++k) ir[s][k] = __dmul_rn(diag, d[s][k]);
     e[s] = blk[s].advance(1);
   }
-  if constexpr (WC > 0) gen_terms<TW, BSMEM, NS, WC>(lp, e, ir);
+  if constexpr (WC > 0) gen_terms<TW, BSMEM, NS, WC, FMA>(lp, e, ir);
   if constexpr (WC >= 0) W = 0;
   if constexpr (NS == 1 && PIPE) {
-    if (W >= 8) gen_terms_pipelined<TW, BSMEM, NS>(lp, e, W, ir);   // leaves W < 4
+    if (W >= 8) gen_terms_pipelined<TW, BSMEM, NS, FMA>(lp, e, W, ir);   // leaves W < 4
   }
   for (; W >= 4; W -= 4) {
-    gen_terms<TW, BSMEM, NS, 4>(lp, e, ir);
+    gen_terms<TW, BSMEM, NS, 4, FMA>(lp, e, ir);
 #pragma unroll
     for (int s = 0; s < NS; ++s) e[s] = e[s].advance(4);
   }
   switch (W) {   // warp-uniform
-    case 3: gen_terms<TW, BSMEM, NS, 3>(lp, e, ir); break;
-    case 2: gen_terms<TW, BSMEM, NS, 2>(lp, e, ir); break;
-    case 1: gen_terms<TW, BSMEM, NS, 1>(lp, e, ir); break;
+    case 3: gen_terms<TW, BSMEM, NS, 3, FMA>(lp, e, ir); break;
+    case 2: gen_terms<TW, BSMEM, NS, 2, FMA>(lp, e, ir); break;
+    case 1: gen_terms<TW, BSMEM, NS, 1, FMA>(lp, e, ir); break;
     default: break;
   }
 #pragma unroll
@@ -225,12 +228,12 @@ __device__ __forceinline__ void gen_x_n(uint32_t lp, const int4 (&own)[NS], cons
     for (int k = 0; k < 4; ++k) x[s][k] = __dadd_rn(d[s][k], __dmul_rn(d[s][k], __dadd_rn(rr[s], ir[s][k])));
 }
 
-template <int TW, bool BSMEM, int WC = -1, bool PIPE = false>
+template <int TW, bool BSMEM, int WC = -1, bool PIPE = false, bool FMA = true>
 __device__ __forceinline__ void gen_x(uint32_t lp, const int4 own, const RecCol<TW, BSMEM>& blk, uint32_t W, double x[4]) {
   const int4 o1[1] = {own};
   const RecCol<TW, BSMEM> b1[1] = {blk};
   double x1[1][4];
-  gen_x_n<TW, BSMEM, 1, WC, PIPE>(lp, o1, b1, W, x1);
+  gen_x_n<TW, BSMEM, 1, WC, PIPE, FMA>(lp, o1, b1, W, x1);
   x[0] = x1[0][0]; x[1] = x1[0][1]; x[2] = x1[0][2]; x[3] = x1[0][3];
 }
 
@@ -290,7 +293,7 @@ __device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t*
 // ---------------------------------------------------------------------------------------------------------
 // NS = 2 (uniform-width beta stream only, p.uslots != 0): a consumer warp takes two adjacent blocks of species rows at a
 // time and runs them as one instruction stream -- twice the independent work per warp for the same number of warps.
-template <int TW, int NW, bool BSMEM, int NS = 1>
+template <int TW, int NW, bool BSMEM, int NS = 1, bool FMA = true>
 __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -352,14 +355,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
         int4 own[2];
         own[0] = lds128i(a0);
         own[1] = lds128i(a0 + R * TW * 4u);
-#ifndef ECO_GEN_NOSKIP
+        // n = 0 stays 0 (x = 0 + 0*(...) = 0, ROUND(0) = 0): a pair whose 256 densities are all extinct is skipped
         if (!__any_sync(FULL, (own[0].x | own[0].y | own[0].z | own[0].w | own[1].x | own[1].y | own[1].z | own[1].w) != 0)) continue;
-#endif
         RecCol<TW, BSMEM> blk[2];
         blk[0].a = strm_s + b0 * blk_bytes; blk[0].p = p.stream + (size_t)b0 * uslots * R + rr;
         blk[1].a = blk[0].a + blk_bytes;    blk[1].p = blk[0].p + (size_t)uslots * R;
         double x[2][4];
-        gen_x_n<TW, BSMEM, 2, WC>(lp, own, blk, W, x);
+        gen_x_n<TW, BSMEM, 2, WC, false, FMA>(lp, own, blk, W, x);
         const uint32_t row0 = b0 * R + rr;
         const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row0 + R, (uint32_t)p.t0, p.rk);
         int4 o0, o1;
@@ -374,7 +376,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
           RecCol<TW, BSMEM> blk;
           blk.a = strm_s + b * blk_bytes; blk.p = p.stream + (size_t)b * uslots * R + rr;
           double x[4];
-          gen_x<TW, BSMEM, -1, true>(lp, own, blk, W, x);
+          gen_x<TW, BSMEM, -1, true, FMA>(lp, own, blk, W, x);
           const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
           __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
         }
@@ -388,8 +390,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
     };
     switch (W) {   // kernel-uniform
       case 3: consume(std::integral_constant<int, 3>{}); break;   // the scripts' random_interaction(3,0)
-      case 2: consume(std::integral_constant<int, 2>{}); break;
-      case 4: consume(std::integral_constant<int, 4>{}); break;
       default: consume(std::integral_constant<int, -1>{}); break;
     }
     return;
@@ -418,18 +418,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       blk.a = strm_s + s0 * (R * 16u);
       blk.p = p.stream + (size_t)s0 * R + rr;
       double x[4];
-#ifndef ECO_ABLATE
-      gen_x<TW, BSMEM, -1, true>(lp, own, blk, W, x);
+      gen_x<TW, BSMEM, -1, true, FMA>(lp, own, blk, W, x);
       const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
       __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
-#else   // cost-attribution builds (tools/ablate.sh): results are wrong on purpose, never shipped
-      gen_x<TW, BSMEM, -1, true>(lp, own, blk, (ECO_ABLATE & 2) ? 0u : W, x);
-      const uint4 u = (ECO_ABLATE & 1) ? make_uint4(row, row * 3u, xq, yg) : philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk);
-      int4 o;
-      if (ECO_ABLATE & 4) o = make_int4(__double2loint(x[0]) ^ u.x, __double2loint(x[1]) ^ u.y, __double2loint(x[2]) ^ u.z, __double2loint(x[3]) ^ u.w);
-      else o = round4(x, u);
-      if (!(ECO_ABLATE & 8) || o.x == 0x7fffffff) __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
-#endif
     }
     first += NW - nbm;
     if (first >= NW) first -= NW;
@@ -444,7 +435,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
 // over niter -- the scripts' cadence is generate(100), models/spatial_ecolab.py:67), CTA-wide barrier per step.
 // ---------------------------------------------------------------------------------------------------------
 // WC >= 0: uniform-width stream of WC terms per row (p.uslots == WC + 1): no offset table, one straight-line term body.
-template <int TW, int THREADS, bool BSMEM, int WC = -1>
+template <int TW, int THREADS, bool BSMEM, int WC = -1, bool FMA = true>
 __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int R = LaneMap<TW>::ROWS;
@@ -498,7 +489,7 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
           blk.a = strm_s + s0 * (R * 16u);
           blk.p = strm + (size_t)s0 * R + rr;
           double x[4];
-          gen_x<TW, BSMEM, WC>(lp, own, blk, W, x);
+          gen_x<TW, BSMEM, WC, false, FMA>(lp, own, blk, W, x);
           o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0 + step, p.rk));
         }
         asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(lq + row * (TW * 4u)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");

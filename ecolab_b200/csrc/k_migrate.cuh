@@ -6,34 +6,20 @@
 // The pairwise term T(a,b) = trunc(cm*(a-b)) is antisymmetric (fl(c*(-d)) = -fl(c*d) and truncation is
 // symmetric about zero), so every flux is evaluated ONCE and applied with opposite signs to its two
 // cells: a warp owns one block of species rows of one tile column and walks down the grid rows
-// carrying, in registers, the current row's densities, its north fluxes and its horizontal net flux.
-// Every density is therefore loaded from memory exactly once (16-byte vectors, 512 contiguous
-// bytes per warp) and written once: 8 B of traffic per cell-species update.
+// carrying, in registers, the current row's densities and its north fluxes.  Every density is loaded
+// from HBM exactly once and written once: 8 B of traffic per cell-species update.
+//
+// Two kernels share that arithmetic:
+//   migrate_pipe_kernel  (default, TW >= 8): a CTA walks down ONE tile column in lock-step.  A producer lane streams
+//                        the grid rows of the CTA's species-row group (16 KiB contiguous per grid row at 1024 species)
+//                        into a shared-memory ring with bulk (TMA-unit) copies; 16 consumer warps take their 512-byte
+//                        pieces out of the ring.  Bytes in flight are set by the ring depth, not by registers, and the
+//                        warps of a CTA cannot drift apart in y (round 1's walker showed 25.7-32 ms launch to launch
+//                        at C4 because they did).
+//   migrate_kernel       (fallback: TW = 4, i.e. more than 2048 species): each warp walks alone with five rows in
+//                        flight in registers.
 #pragma once
 #include "k_common.cuh"
-
-#ifndef ECO_MIG_MINB
-#define ECO_MIG_MINB 2     // resident CTAs per SM the register budget is set for (2 x 256 threads -> up to 128 registers)
-#endif
-#ifndef ECO_MIG_NB
-#define ECO_MIG_NB 5       // grid rows a warp keeps in flight in registers.  Measured on C3 (ms): NB/CTAs per SM =
-                           // 2/4: 2.03 (spills)  2/3: 1.68  3/3: 2.03 (spills)  3/2: 1.73  4/2: 1.63  5/2: 1.61  6/2: 1.89  8/1: 2.04
-#endif
-#ifndef ECO_MIG_ALIAS
-#define ECO_MIG_ALIAS 1    // extra-cell loads unpredicated (measured on C3: 1.85 ms, predicated 1.96 ms)
-#endif
-#ifndef ECO_MIG_STCS
-#define ECO_MIG_STCS 1     // 1: streaming (evict-first) stores (with 5 rows in flight: 1.60 vs 1.61 ms)
-#endif
-#ifndef ECO_MIG_LDCS
-#define ECO_MIG_LDCS 0     // 1: streaming loads of the lane's vector
-#endif
-#ifndef ECO_MIG_THREADS
-#define ECO_MIG_THREADS 256
-#endif
-#ifndef ECO_MIG_PF
-#define ECO_MIG_PF 0      // grid rows between an L2 prefetch and the register load of a row; 0 = none (per-lane prefetches in the earlier kernel: 4/8/16 rows ahead all SLOWER, 2.3-2.6 vs 1.85 ms on C3); now counted in trips of ECO_MIG_NB rows, bulk prefetch per warp row
-#endif
 
 namespace eco {
 
@@ -44,6 +30,15 @@ struct MigParams {
   const int32_t* bottom_row;  // grid row y0+ny
   const double* cm;           // [cap] capped migration coefficient per species row (0 for padding rows)
   uint32_t yseg, nseg;        // grid rows per work unit, units along y
+  uint32_t gb, ngroups;       // pipe kernel: species-row blocks per unit, units per tile
+  uint32_t capblk;            // pipe kernel: cap / (species rows per warp-op)
+  uint32_t nstages;           // pipe kernel: ring depth (grid rows in flight per CTA)
+  // multi-GPU, peer rows read over NVLink (null = ghost rows already filled): the neighbour ranks' "generate done"
+  // epoch counters; a boundary unit's producer waits until the counter reaches `epoch` before it copies the peer's row
+  const unsigned int* top_flag;
+  const unsigned int* bottom_flag;
+  unsigned int epoch;
+  unsigned int* err;          // set to 1 if a flag wait timed out
   unsigned long long* total;
 };
 
@@ -57,27 +52,19 @@ __device__ __forceinline__ int flux(double c, double ba, double bb) {
 // Cells across the tile boundary.  A lane on the first (last) quad of its species row loads ONE extra cell per grid
 // row: the last cell of the west tile (first cell of the east tile).  Where the grid has no such neighbour the
 // extra load aliases the lane's own boundary cell, so the difference -- and the flux -- is 0 without any flag
-// (open boundaries, reference :593-600).  Lanes in the middle of a row load nothing extra.
+// (open boundaries, reference :593-600).  Lanes in the middle of a row alias their own first cell (value unused).
 struct MigRow {
   int4 v;      // this lane's 4 cells
   int e;       // west neighbour (first lane of a species row) / east neighbour (last lane)
-  int e2;      // DUALE only (one lane holds a whole species row of the warp's span): east neighbour, `e` is the west one
+  int e2;      // DUALE only (one lane holds a whole species row): east neighbour, `e` is the west one
 };
 
 template <bool DUALE>
-__device__ __forceinline__ MigRow mig_load(const int32_t* p, long long eoff, long long eoff2, bool has_e) {
+__device__ __forceinline__ MigRow mig_load(const int32_t* p, long long eoff, long long eoff2) {
   MigRow m;
-#if ECO_MIG_LDCS
-  m.v = __ldcs(reinterpret_cast<const int4*>(p));
-#else
   m.v = *reinterpret_cast<const int4*>(p);
-#endif
-  m.e = 0; m.e2 = 0;
-#if ECO_MIG_ALIAS
-  m.e = *(p + eoff);                 // every lane loads: lanes in the middle of a row alias their own first cell
-#else
-  if (has_e) m.e = *(p + eoff);
-#endif
+  m.e = *(p + eoff);
+  m.e2 = 0;
   if (DUALE) m.e2 = *(p + eoff2);
   return m;
 }
@@ -105,203 +92,117 @@ __device__ __forceinline__ int4 mig_horizontal(const double (&b)[4], int e, int 
   return make_int4(t0 - t1, t1 - t2, t2 - t3, t3 - tn);
 }
 
-// State a warp carries down the grid rows: the current row as 2^52+n doubles (the low word IS the density),
-// its extra boundary cell(s) and its north fluxes.
-struct MigCarry {
+// State a warp carries down the grid rows: the current row as 2^52+n doubles (the low word IS the density) and its
+// north fluxes.
+struct MigState {
   double b[4];
-  int e, e2;
   int4 tn;
 };
 
-// A freshly loaded row unpacked into the carry's form.  Unpacking is the LAST use of the load's registers, so the
-// caller re-issues the load for a later row right after it and before the row's arithmetic: every load then has
-// two full rows of arithmetic (its own buffer's and the other buffer's) to arrive, not one.
-struct MigNext {
-  double b[4];
-  int e, e2;
-};
-__device__ __forceinline__ MigNext mig_unpack(const MigRow& r) {
-  MigNext x;
-  x.b[0] = big(r.v.x); x.b[1] = big(r.v.y); x.b[2] = big(r.v.z); x.b[3] = big(r.v.w);
-  x.e = r.e; x.e2 = r.e2;
-  return x;
+__device__ __forceinline__ void mig_start(MigState& k, const int4 up, const int4 cur, double c) {
+  k.b[0] = big(cur.x); k.b[1] = big(cur.y); k.b[2] = big(cur.z); k.b[3] = big(cur.w);
+  k.tn = make_int4(flux(c, big(up.x), k.b[0]), flux(c, big(up.y), k.b[1]), flux(c, big(up.z), k.b[2]),
+                   flux(c, big(up.w), k.b[3]));                                             // T(n[y-1] - n[y])
 }
 
-// Finish the current row given the row below it (`nx`), store it, and make `nx` the current row.
+// Finish the current row given the row below it (`nv`) and the current row's extra cell(s), store it, and make `nv`
+// the current row.
 template <bool DUALE, bool RAG>
-__device__ __forceinline__ void mig_finish(MigCarry& k, const MigNext& nx, double c, bool first_q, bool last_q, uint32_t rag,
-                                           int32_t* __restrict__ dp, unsigned long long& acc) {
-#ifdef ECO_MIG_ABLATE   // cost attribution only (wrong results on purpose): the same loads and stores, no flux arithmetic
-  {
-    const int4 o = make_int4(__double2loint(k.b[0]) + nx.e, __double2loint(k.b[1]), __double2loint(k.b[2]), __double2loint(k.b[3]) + k.e);
-    *reinterpret_cast<int4*>(dp) = o;
-    k.b[0] = nx.b[0]; k.b[1] = nx.b[1]; k.b[2] = nx.b[2]; k.b[3] = nx.b[3];
-    k.e = nx.e;
-    return;
-  }
-#endif
+__device__ __forceinline__ void mig_finish(MigState& k, const int4 nv, int e, int e2, double c, bool first_q, bool last_q,
+                                           uint32_t rag, int32_t* __restrict__ dp, unsigned long long& acc) {
+  const double nb[4] = {big(nv.x), big(nv.y), big(nv.z), big(nv.w)};
   // north flux of the row below = minus the south flux of this row
-  const int4 ts = make_int4(flux(c, k.b[0], nx.b[0]), flux(c, k.b[1], nx.b[1]), flux(c, k.b[2], nx.b[2]), flux(c, k.b[3], nx.b[3]));
-  const int4 hs = mig_horizontal<DUALE, RAG>(k.b, k.e, k.e2, c, first_q, last_q, rag);
+  const int4 ts = make_int4(flux(c, k.b[0], nb[0]), flux(c, k.b[1], nb[1]), flux(c, k.b[2], nb[2]), flux(c, k.b[3], nb[3]));
+  const int4 hs = mig_horizontal<DUALE, RAG>(k.b, e, e2, c, first_q, last_q, rag);
   const int d0 = k.tn.x - ts.x + hs.x, d1 = k.tn.y - ts.y + hs.y, d2 = k.tn.z - ts.z + hs.z, d3 = k.tn.w - ts.w + hs.w;
   const int4 out = make_int4(__double2loint(k.b[0]) + d0, __double2loint(k.b[1]) + d1, __double2loint(k.b[2]) + d2,
                              __double2loint(k.b[3]) + d3);
-#if ECO_MIG_STCS
-  __stcs(reinterpret_cast<int4*>(dp), out);
-#else
-  *reinterpret_cast<int4*>(dp) = out;
-#endif
+  __stcs(reinterpret_cast<int4*>(dp), out);   // streaming (evict-first): the row is not read again by this kernel
   acc += (unsigned long long)((uint32_t)abs(d0) + (uint32_t)abs(d1)) + (unsigned long long)((uint32_t)abs(d2) + (uint32_t)abs(d3));
-  k.b[0] = nx.b[0]; k.b[1] = nx.b[1]; k.b[2] = nx.b[2]; k.b[3] = nx.b[3];
-  k.e = nx.e; k.e2 = nx.e2; k.tn = ts;
-}
-template <bool DUALE, bool RAG>
-__device__ __forceinline__ void mig_step(MigCarry& k, const MigRow& nxt, double c, bool first_q, bool last_q, uint32_t rag,
-                                         int32_t* __restrict__ dp, unsigned long long& acc) {
-  mig_finish<DUALE, RAG>(k, mig_unpack(nxt), c, first_q, last_q, rag, dp, acc);
+  k.b[0] = nb[0]; k.b[1] = nb[1]; k.b[2] = nb[2]; k.b[3] = nb[3];
+  k.tn = ts;
 }
 
-// A work unit = one block of species rows x one tile column x n grid rows.  The rows of the unit are streamed as
-// the sequence  north, row(0), ..., row(n-1), south  where `north` / `south` are the rows just outside the unit
-// (ghost rows or a peer GPU's boundary rows at the slab ends) or, at the edge of the GLOBAL grid, the unit's own
-// first / last row again (difference 0 -> flux 0).  Loads run two rows ahead of the arithmetic (see MigNext); the
-// main loop (two rows per trip, no register rotation) has no boundary cases.
+// =====================================================================================================================
+// fallback: the register walker.  A work unit = one block of species rows x one tile x n grid rows, streamed as the
+// sequence  north, row(0), ..., row(n-1), south  where `north` / `south` are the rows just outside the unit (ghost
+// rows or a peer GPU's boundary rows at the slab ends) or, at the edge of the GLOBAL grid, the unit's own first / last
+// row again (difference 0 -> flux 0).  NB rows are in flight per warp in registers; a row's load is re-issued the
+// moment the row is unpacked.
+// =====================================================================================================================
+constexpr int kMigThreads = 256;
+constexpr int kMigRowsInFlight = 5;   // measured on C3 (ms): 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04 (round 1)
+
 template <bool DUALE, bool RAG, int NB>
 __device__ __forceinline__ void mig_unit(const int32_t* __restrict__ p0, const int32_t* __restrict__ pn,
                                          const int32_t* __restrict__ ps, int32_t* __restrict__ dp, long long stride, uint32_t n,
-                                         long long eoff, long long eoff2, bool has_e, double c, bool first_q, bool last_q,
-                                         uint32_t rag, unsigned long long& acc) {
+                                         long long eoff, long long eoff2, double c, bool first_q, bool last_q, uint32_t rag,
+                                         unsigned long long& acc) {
   auto rowp = [&](uint32_t r) -> const int32_t* { return r < n ? p0 + (long long)r * stride : ps; };
   const int4 up = *reinterpret_cast<const int4*>(pn);
-  const MigRow first = mig_load<DUALE>(p0, eoff, eoff2, has_e);
+  const MigRow first = mig_load<DUALE>(p0, eoff, eoff2);
   MigRow r[NB];                                                                             // rows i+1 .. i+NB, in flight
 #pragma unroll
-  for (int j = 0; j < NB; ++j) r[j] = mig_load<DUALE>(rowp(1 + j), eoff, eoff2, has_e);
-  MigCarry k;
-  k.b[0] = big(first.v.x); k.b[1] = big(first.v.y); k.b[2] = big(first.v.z); k.b[3] = big(first.v.w);
-  k.e = first.e; k.e2 = first.e2;
-  k.tn = make_int4(flux(c, big(up.x), k.b[0]), flux(c, big(up.y), k.b[1]), flux(c, big(up.z), k.b[2]),
-                   flux(c, big(up.w), k.b[3]));                                             // T(n[y-1] - n[y])
+  for (int j = 0; j < NB; ++j) r[j] = mig_load<DUALE>(rowp(1 + j), eoff, eoff2);
+  MigState k;
+  mig_start(k, up, first.v, c);
+  int e = first.e, e2 = first.e2;
   uint32_t i = 0;
   const int32_t* pl = p0 + (long long)(NB + 1) * stride;                                    // row(i+NB+1)
-#if ECO_MIG_PF > 0   // experiment (warp span T = 1 only): the warp's 512-byte rows requested into L2 ECO_MIG_PF trips ahead, one bulk prefetch per row
-  const uint32_t pf_lane = threadIdx.x & 31u;
-  const int32_t* wb = p0 - 4 * pf_lane;
-  if (pf_lane < ECO_MIG_PF * NB && NB + 1 + pf_lane < n) bulk_prefetch_l2(wb + (long long)(NB + 1 + pf_lane) * stride, 512u);
-#endif
   for (; i + 2 * NB < n; i += NB) {                                                         // NB rows per trip, no register rotation
-#if ECO_MIG_PF > 0
-    if (pf_lane < NB) {
-      const uint32_t pr = i + NB + 1 + ECO_MIG_PF * NB + pf_lane;
-      if (pr < n) bulk_prefetch_l2(wb + (long long)pr * stride, 512u);
-    }
-#endif
 #pragma unroll
     for (int j = 0; j < NB; ++j) {
-      const MigNext nx = mig_unpack(r[j]);
-      r[j] = mig_load<DUALE>(pl + (long long)j * stride, eoff, eoff2, has_e);
-      mig_finish<DUALE, RAG>(k, nx, c, first_q, last_q, rag, dp + (long long)j * stride, acc);
+      const MigRow nx = r[j];
+      r[j] = mig_load<DUALE>(pl + (long long)j * stride, eoff, eoff2);
+      mig_finish<DUALE, RAG>(k, nx.v, e, e2, c, first_q, last_q, rag, dp + (long long)j * stride, acc);
+      e = nx.e; e2 = nx.e2;
     }
     pl += (long long)NB * stride;
     dp += (long long)NB * stride;
   }
 #pragma unroll 1
   for (; i < n; ++i) {                                                                      // at most 2*NB rows
-    const MigNext nx = mig_unpack(r[0]);
+    const MigRow nx = r[0];
 #pragma unroll
     for (int j = 0; j + 1 < NB; ++j) r[j] = r[j + 1];
-    r[NB - 1] = mig_load<DUALE>(rowp(i + NB + 1), eoff, eoff2, has_e);
-    mig_finish<DUALE, RAG>(k, nx, c, first_q, last_q, rag, dp, acc);
+    r[NB - 1] = mig_load<DUALE>(rowp(i + NB + 1), eoff, eoff2);
+    mig_finish<DUALE, RAG>(k, nx.v, e, e2, c, first_q, last_q, rag, dp, acc);
+    e = nx.e; e2 = nx.e2;
     dp += stride;
   }
 }
 
-// ---- the same unit with a per-warp shared-memory ring instead of the two register rows -------------------------------
-// Each lane copies its 16 bytes (+ its extra cell) of the next ECO_MIG_RING grid rows into a private slot with cp.async
-// (LDGSTS: no registers held while the load is in flight) and reads it back when the row's turn comes.  Bytes in flight
-// per warp: ECO_MIG_RING x 640 instead of 2 x 640.  A lane only ever touches its own slot bytes: no barrier, only
-// cp.async.wait_group.  Slot = 512 B of vectors + 128 B of extra cells.
-#ifndef ECO_MIG_RING
-#define ECO_MIG_RING 0
-#endif
-constexpr uint32_t kMigSlotBytes = 640;
-
-__device__ __forceinline__ void mig_cp_row(uint32_t sv, uint32_t se, const int32_t* p, long long eoff, bool has_e) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sv), "l"(p) : "memory");
-  if (has_e) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(se), "l"(p + eoff) : "memory");
-  asm volatile("cp.async.commit_group;" ::: "memory");
+// element offsets of a lane's extra cell(s) relative to its vector: west tile's last cell | own cell 0, east tile's
+// first cell | own cell 3
+__device__ __forceinline__ void mig_edge_offsets(const Layout& L, uint32_t x0, uint32_t tw, long long& eo_w, long long& eo_e) {
+  const bool has_l = x0 > 0, has_r = x0 + 4 < L.nx;
+  eo_w = has_l ? (long long)(tw - 1) - (long long)L.tile_stride : 0;
+  eo_e = has_r ? (long long)L.tile_stride - (long long)(tw - 4) : 3;
 }
 
-template <bool RAG, int D>
-__device__ __forceinline__ void mig_unit_ring(const int32_t* __restrict__ p0, const int32_t* __restrict__ pn,
-                                              const int32_t* __restrict__ ps, int32_t* __restrict__ dp, long long stride,
-                                              uint32_t n, long long eoff, bool has_e, double c, bool first_q, bool last_q,
-                                              uint32_t rag, uint32_t sv0, uint32_t se0, unsigned long long& acc) {
-  auto rowp = [&](uint32_t r) -> const int32_t* { return r < n ? p0 + (long long)r * stride : ps; };
-#pragma unroll
-  for (int k = 0; k < D; ++k) mig_cp_row(sv0 + k * kMigSlotBytes, se0 + k * kMigSlotBytes, rowp(k + 1), eoff, has_e);
-  const int4 up = *reinterpret_cast<const int4*>(pn);
-  const MigRow first = mig_load<false>(p0, eoff, 0, has_e);
-  MigCarry k;
-  k.b[0] = big(first.v.x); k.b[1] = big(first.v.y); k.b[2] = big(first.v.z); k.b[3] = big(first.v.w);
-  k.e = first.e; k.e2 = 0;
-  k.tn = make_int4(flux(c, big(up.x), k.b[0]), flux(c, big(up.y), k.b[1]), flux(c, big(up.z), k.b[2]),
-                   flux(c, big(up.w), k.b[3]));                                             // T(n[y-1] - n[y])
-  const int32_t* pl = rowp(D + 1);
-  uint32_t so = 0;                                                                          // byte offset of the slot of row(i+1)
-  for (uint32_t i = 0; i < n; ++i) {
-    asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
-    MigRow nxt;
-    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(nxt.v.x), "=r"(nxt.v.y), "=r"(nxt.v.z), "=r"(nxt.v.w) : "r"(sv0 + so) : "memory");
-    nxt.e = 0; nxt.e2 = 0;
-    if (has_e) asm volatile("ld.shared.s32 %0, [%1];" : "=r"(nxt.e) : "r"(se0 + so) : "memory");
-    mig_step<false, RAG>(k, nxt, c, first_q, last_q, rag, dp, acc);
-    mig_cp_row(sv0 + so, se0 + so, pl, eoff, has_e);                                        // row(i+1+D), clamped to `south`
-    pl = i + 2 + D < n ? pl + stride : ps;
-    so = so + kMigSlotBytes == D * kMigSlotBytes ? 0u : so + kMigSlotBytes;
-    dp += stride;
-  }
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-}
-
-// Lane map: a warp spans T adjacent tiles of one grid row: lane = (species row * T + tile) * QPR + quad, i.e. the
-// LPR = T*QPR lanes of one species row hold 4*LPR CONSECUTIVE cells, neighbours across a tile boundary inside the span
-// are one shuffle away, and only the two end lanes of a row load an extra cell (one 32-byte sector each).  T = 1 is
-// the generate kernel's map (512 contiguous bytes per warp); larger T trades contiguity (32/T rows x 64 B per tile) for
-// fewer extra sectors: per warp-row 2*32/LPR of them.  The host picks T (p.L.ntx must be a multiple of it).
-template <int TW, int T>
-__global__ void __launch_bounds__(ECO_MIG_THREADS, ECO_MIG_MINB) migrate_kernel(const MigParams p) {
-  constexpr int QPR = TW / 4, LPR = QPR * T, RW = 32 / LPR;   // lanes per species row, species rows per warp
-  constexpr bool DUALE = LPR == 1;
-  static_assert(LPR <= 32 && 32 % LPR == 0, "span wider than a warp");
+template <int TW>
+__global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams p) {
+  constexpr int QPR = TW / 4, RW = 32 / QPR;   // lanes per species row, species rows per warp
+  constexpr bool DUALE = QPR == 1;
   const Layout& L = p.L;
   const uint32_t lane = threadIdx.x & 31u, wpb = blockDim.x >> 5;
-  const uint32_t rr = lane / LPR, t = (lane % LPR) / QPR, q = lane % QPR;
-  const uint32_t ngroups = L.ntx / T, nrowblk = (L.nsp + RW - 1) / RW;
-  const unsigned long long nunits = (unsigned long long)p.nseg * ngroups * nrowblk;
+  const uint32_t rr = lane / QPR, q = lane % QPR;
+  const uint32_t nrowblk = (L.nsp + RW - 1) / RW;
+  const unsigned long long nunits = (unsigned long long)p.nseg * L.ntx * nrowblk;
   const long long stride = (long long)L.row_stride;
-  const bool first_q = lane % LPR == 0, last_q = lane % LPR == LPR - 1;
-  const bool has_e = first_q || last_q;
-#if ECO_MIG_RING > 0
-  extern __shared__ __align__(16) unsigned char mig_smem[];
-  const uint32_t sv0 = smem_u32(mig_smem) + (threadIdx.x >> 5) * (ECO_MIG_RING * kMigSlotBytes) + lane * 16u;
-  const uint32_t se0 = sv0 - lane * 16u + 512u + lane * 4u;
-#endif
+  const bool first_q = q == 0, last_q = q == QPR - 1;
   unsigned long long acc = 0;
   for (unsigned long long w = (unsigned long long)blockIdx.x * wpb + (threadIdx.x >> 5); w < nunits;
        w += (unsigned long long)gridDim.x * wpb) {
     const uint32_t b = (uint32_t)(w % nrowblk);
-    const uint32_t g = (uint32_t)((w / nrowblk) % ngroups);
-    const uint32_t seg = (uint32_t)(w / ((unsigned long long)nrowblk * ngroups));
+    const uint32_t tx = (uint32_t)((w / nrowblk) % L.ntx);
+    const uint32_t seg = (uint32_t)(w / ((unsigned long long)nrowblk * L.ntx));
     const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
     const uint32_t row = min(b * RW + rr, L.cap - 1);      // cap is a multiple of 32: the clamp never triggers, it bounds the address
-    const uint32_t tx = g * T + t;
     const double c = __ldg(p.cm + row);
     const uint32_t x0 = tx * TW + 4 * q;
-    const bool has_l = x0 > 0, has_r = x0 + 4 < L.nx;
-    // element offsets of the extra cell(s) relative to the lane's vector
-    const long long eo_w = has_l ? (long long)(TW - 1) - (long long)L.tile_stride : 0;   // west tile's last cell | own cell 0
-    const long long eo_e = has_r ? (long long)L.tile_stride - (long long)(TW - 4) : 3;   // east tile's first cell | own cell 3
+    long long eo_w, eo_e;
+    mig_edge_offsets(L, x0, TW, eo_w, eo_e);
     const long long eoff = (DUALE || first_q) ? eo_w : (last_q ? eo_e : 0);
     const size_t lane_off = (size_t)tx * L.tile_stride + (size_t)row * TW + 4 * q;
     const int32_t* p0 = L.base + (size_t)ys * L.row_stride + lane_off;                      // row(0)
@@ -309,17 +210,194 @@ __global__ void __launch_bounds__(ECO_MIG_THREADS, ECO_MIG_MINB) migrate_kernel(
     const int32_t* ps = L.y0 + ye >= L.nyg ? p0 + (long long)(n - 1) * stride
                                            : (ye == L.ny ? p.bottom_row + lane_off : p0 + (long long)n * stride);
     int32_t* dp = p.dst + (size_t)ys * L.row_stride + lane_off;
-    const bool ragged = (g + 1) * T * TW > L.nx;   // warp-uniform: the span contains the ragged last tile
+    const bool ragged = (tx + 1) * TW > L.nx;      // warp-uniform: the ragged last tile
     const uint32_t rag = 1u + (x0 >= L.nx ? 0u : min(5u, L.nx - x0));
-#if ECO_MIG_RING > 0
-    if (!DUALE) {
-      if (ragged) mig_unit_ring<true, ECO_MIG_RING>(p0, pn, ps, dp, stride, n, eoff, has_e, c, first_q, last_q, rag, sv0, se0, acc);
-      else mig_unit_ring<false, ECO_MIG_RING>(p0, pn, ps, dp, stride, n, eoff, has_e, c, first_q, last_q, 0u, sv0, se0, acc);
-      continue;
+    if (ragged) mig_unit<DUALE, true, kMigRowsInFlight>(p0, pn, ps, dp, stride, n, eoff, eo_e, c, first_q, last_q, rag, acc);
+    else mig_unit<DUALE, false, kMigRowsInFlight>(p0, pn, ps, dp, stride, n, eoff, eo_e, c, first_q, last_q, 0u, acc);
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);
+  if (lane == 0 && acc) atomicAdd(p.total, acc);
+}
+
+// =====================================================================================================================
+// default: the tile-column pipeline.
+//   unit      = (y segment, tile column tx, group g of `gb` = NW*NS consecutive species-row blocks): per grid row the
+//               group is ONE contiguous piece of the tile, gb x 512 bytes;
+//   warp NW   = producer: one lane streams  north, row(0) .. row(n-1), south  of the unit into a ring of `nstages`
+//               shared-memory slots with one bulk copy per grid row ("full" mbarriers), re-filling a slot as soon as
+//               all consumer warps have released it ("empty" mbarriers); the ring runs on across unit boundaries;
+//   warps 0..NW-1 = consumers: warp w owns blocks g*gb + w*NS + {0..NS-1} for the whole walk, takes its 512-byte
+//               pieces of every row out of the ring and keeps the current row + north fluxes in registers; the
+//               extra cells across the tile boundary (one per species row and side) come straight from global memory,
+//               KE rows ahead; results go from registers to HBM as 16-byte streaming stores (512 B per warp-op).
+// Units are numbered group-fastest, then tile column, then segment, so the CTAs resident at one time cover adjacent
+// tile columns of the same rows: the extra-cell sectors they read from each other's tiles are L2 hits.
+// =====================================================================================================================
+constexpr int kMigPipeWarps = 16;     // consumer warps
+constexpr int kMigPipeEdge = 4;       // rows the extra-cell loads run ahead
+
+// publish this rank's epoch counter to the neighbour ranks (they map it through CUDA IPC)
+__global__ void flag_publish_kernel(unsigned int* flag, unsigned int value) {
+  __threadfence_system();   // everything this stream did before is visible to the peers before the counter moves
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
+// poll a neighbour rank's "generate done" counter (peer memory over NVLink); bounded so that a lost peer cannot hang the GPU
+__device__ __forceinline__ void mig_wait_flag(const unsigned int* flag, unsigned int epoch, unsigned int* err) {
+  const long long t0 = clock64();
+  for (;;) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if ((int)(v - epoch) >= 0) return;
+    if (clock64() - t0 > 4000000000ll) { atomicExch(err, 1u); return; }   // ~2 s
+    __nanosleep(200);
+  }
+}
+
+template <int TW, int NS, bool RAG>
+__device__ __forceinline__ void migp_unit(const MigParams& p, uint32_t tx, uint32_t g, uint32_t ys, uint32_t n, uint32_t warp,
+                                          uint32_t lane, uint32_t ring_s, uint32_t full_s, uint32_t empty_s, uint32_t stage_bytes,
+                                          uint32_t& stage, uint32_t& phase, unsigned long long& acc) {
+  constexpr int QPR = TW / 4, RW = 32 / QPR, KE = kMigPipeEdge;
+  const Layout& L = p.L;
+  const uint32_t rr = lane / QPR, q = lane % QPR;
+  const bool first_q = q == 0, last_q = q == QPR - 1;
+  const long long stride = (long long)L.row_stride;
+  const uint32_t x0 = tx * TW + 4 * q;
+  const uint32_t rag = 1u + (x0 >= L.nx ? 0u : min(5u, L.nx - x0));
+  long long eo_w, eo_e;
+  mig_edge_offsets(L, x0, TW, eo_w, eo_e);
+  const long long eoff = first_q ? eo_w : (last_q ? eo_e : 0);
+
+  bool valid[NS];
+  double c[NS];
+  const int32_t* ep[NS];   // this lane's extra cell of row(i + KE)
+  int32_t* dp[NS];
+  uint32_t soff[NS];
+  int e[NS][KE];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) {
+    const uint32_t lb = warp * NS + s, blk = g * p.gb + lb;
+    valid[s] = blk < p.capblk;
+    const uint32_t row = min(blk * RW + rr, L.cap - 1);
+    c[s] = __ldg(p.cm + row);
+    const size_t lane_off = (size_t)tx * L.tile_stride + (size_t)row * TW + 4 * q;
+    const int32_t* p0 = L.base + (size_t)ys * L.row_stride + lane_off;
+    dp[s] = p.dst + (size_t)ys * L.row_stride + lane_off;
+    soff[s] = lb * 512u + lane * 16u;
+#pragma unroll
+    for (int j = 0; j < KE; ++j) e[s][j] = (valid[s] && (uint32_t)j < n) ? __ldg(p0 + eoff + (long long)j * stride) : 0;
+    ep[s] = p0 + eoff + (long long)KE * stride;
+  }
+
+  // one ring slot: wait until the row has landed, take this warp's pieces, release the slot
+  auto next_row = [&](int4 (&v)[NS]) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(full_s + 8u * stage), "r"(phase) : "memory");
+    const uint32_t a = ring_s + stage * stage_bytes;
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+      asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v[s].x), "=r"(v[s].y), "=r"(v[s].z), "=r"(v[s].w) : "r"(a + soff[s]) : "memory");
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_s + 8u * stage) : "memory");
+    if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
+  };
+
+  int4 up[NS], cur[NS], nv[NS];
+  next_row(up);
+  next_row(cur);
+  MigState k[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) mig_start(k[s], up[s], cur[s], c[s]);
+
+  uint32_t i = 0;
+  for (; i + KE <= n; i += KE) {
+#pragma unroll
+    for (int j = 0; j < KE; ++j) {
+      next_row(nv);
+#pragma unroll
+      for (int s = 0; s < NS; ++s) {
+        if (valid[s]) {
+          const int ec = e[s][j];
+          if (i + j + KE < n) e[s][j] = __ldg(ep[s]);
+          mig_finish<false, RAG>(k[s], nv[s], ec, 0, c[s], first_q, last_q, rag, dp[s], acc);
+        }
+        ep[s] += stride;
+        dp[s] += stride;
+      }
     }
-#endif
-    if (ragged) mig_unit<DUALE, true, ECO_MIG_NB>(p0, pn, ps, dp, stride, n, eoff, eo_e, has_e, c, first_q, last_q, rag, acc);
-    else mig_unit<DUALE, false, ECO_MIG_NB>(p0, pn, ps, dp, stride, n, eoff, eo_e, has_e, c, first_q, last_q, 0u, acc);
+  }
+#pragma unroll 1
+  for (; i < n; ++i) {                                   // fewer than KE rows left: every extra cell is already in e[]
+    next_row(nv);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      if (valid[s]) mig_finish<false, RAG>(k[s], nv[s], e[s][0], 0, c[s], first_q, last_q, rag, dp[s], acc);
+#pragma unroll
+      for (int j = 0; j + 1 < KE; ++j) e[s][j] = e[s][j + 1];
+      dp[s] += stride;
+    }
+  }
+}
+
+template <int TW, int NS>
+__global__ void __launch_bounds__((kMigPipeWarps + 1) * 32, 1) migrate_pipe_kernel(const MigParams p) {
+  extern __shared__ __align__(128) unsigned char mig_smem[];
+  constexpr int NW = kMigPipeWarps;
+  static_assert(TW >= 8, "one lane per species row needs the walker");
+  const Layout& L = p.L;
+  const uint32_t S = p.nstages, stage_bytes = p.gb * 512u;
+  uint64_t* full = reinterpret_cast<uint64_t*>(mig_smem + (size_t)S * stage_bytes);
+  uint64_t* empty = full + S;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, NW); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint32_t per_seg = L.ntx * p.ngroups, nunits = p.nseg * per_seg;
+
+  if (warp == NW) {
+    if (lane == 0) {
+      uint32_t stage = 0, round = 0;
+      for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const uint32_t g = u % p.ngroups, tx = (u / p.ngroups) % L.ntx, seg = u / per_seg;
+        const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
+        const uint32_t bytes = min(p.gb, p.capblk - g * p.gb) * 512u;
+        const size_t off = (size_t)tx * L.tile_stride + (size_t)g * p.gb * 128u;            // a block is 128 ints of a tile
+        const int32_t* p0 = L.base + (size_t)ys * L.row_stride + off;
+        const bool peer_n = ys == 0 && L.y0 != 0, peer_s = ye == L.ny && L.y0 + ye < L.nyg;
+        const int32_t* pn = L.y0 + ys == 0 ? p0 : (ys == 0 ? p.top_row + off : p0 - (long long)L.row_stride);
+        const int32_t* ps = L.y0 + ye >= L.nyg ? p0 + (size_t)(n - 1) * L.row_stride
+                                               : (ye == L.ny ? p.bottom_row + off : p0 + (size_t)n * L.row_stride);
+        if (peer_n && p.top_flag) mig_wait_flag(p.top_flag, p.epoch, p.err);
+        if (peer_s && p.bottom_flag) mig_wait_flag(p.bottom_flag, p.epoch, p.err);
+        for (uint32_t i = 0; i < n + 2; ++i) {
+          const int32_t* src = i == 0 ? pn : (i == n + 1 ? ps : p0 + (size_t)(i - 1) * L.row_stride);
+          if (round) mbar_wait(empty + stage, (round - 1u) & 1u);
+          mbar_expect_tx(full + stage, bytes);
+          bulk_g2s(mig_smem + (size_t)stage * stage_bytes, src, bytes, full + stage);
+          if (++stage == S) { stage = 0; ++round; }
+        }
+      }
+    }
+    return;
+  }
+
+  const uint32_t ring_s = smem_u32(mig_smem), full_s = smem_u32(full), empty_s = smem_u32(empty);
+  uint32_t stage = 0, phase = 0;
+  unsigned long long acc = 0;
+  for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+    const uint32_t g = u % p.ngroups, tx = (u / p.ngroups) % L.ntx, seg = u / per_seg;
+    const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
+    if ((tx + 1) * TW > L.nx) migp_unit<TW, NS, true>(p, tx, g, ys, n, warp, lane, ring_s, full_s, empty_s, stage_bytes, stage, phase, acc);
+    else migp_unit<TW, NS, false>(p, tx, g, ys, n, warp, lane, ring_s, full_s, empty_s, stage_bytes, stage, phase, acc);
   }
 #pragma unroll
   for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);

@@ -585,6 +585,11 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
     *out = (double)v[std::min(7, std::max(0, s.size() > 10 ? s[10] - '0' : 0))];
   }
   else if (s == "nprocs") *out = (double)m->nprocs;
+  else if (s == "y0") *out = (double)m->y0;
+  else if (s == "ny_local") *out = (double)m->nyl;
+  else if (s == "panmictic") *out = m->panmictic ? 1.0 : 0.0;
+  else if (s == "buf_version") *out = (double)m->eng.buf_version();
+  else if (s == "peer_connected") *out = m->eng.peer_connected() ? 1.0 : 0.0;
   else throw std::runtime_error("unknown scalar member: " + s);
   ECO_CATCH
 }
@@ -637,6 +642,8 @@ int eco_set_density_all(eco_model* m, const int32_t* d, size_t ncells, size_t ns
   if (ncells != m->ncells_local()) throw std::runtime_error("set_density_all: cell count differs from the owned grid");
   m->grow_engine(std::max(nsp, m->nsp()));
   if (nsp != m->eng.nsp()) throw std::runtime_error("set_density_all: species count differs from the model");
+  for (size_t i = 0; i < ncells * nsp; ++i)
+    if (d[i] < 0) throw std::runtime_error("density must be non-negative (reference asserts density>=0, models/ecolab_model.cc:108)");
   m->eng.set_density_all(d, nsp);
   ECO_CATCH
 }
@@ -646,6 +653,25 @@ int eco_get_density_all(eco_model* m, int32_t* out, size_t ncells, size_t nsp) {
   if (ncells != m->ncells_local()) throw std::runtime_error("get_density_all: cell count differs from the owned grid");
   if (nsp != m->eng.nsp()) throw std::runtime_error("get_density_all: species count differs from the model");
   m->eng.get_density_all(out, nsp);
+  ECO_CATCH
+}
+int eco_get_density_rows(eco_model* m, size_t y, size_t nrows, int32_t* out, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (y < m->y0 || y + nrows > m->y0 + m->nyl) throw std::runtime_error("get_density_rows: rows are not owned by this process");
+  if (nsp != m->eng.nsp()) throw std::runtime_error("get_density_rows: species count differs from the model");
+  m->eng.get_density_rows((uint32_t)(y - m->y0), (uint32_t)nrows, out, nsp);
+  ECO_CATCH
+}
+int eco_set_density_rows(eco_model* m, size_t y, size_t nrows, const int32_t* d, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (y < m->y0 || y + nrows > m->y0 + m->nyl) throw std::runtime_error("set_density_rows: rows are not owned by this process");
+  m->grow_engine(std::max(nsp, m->nsp()));
+  if (nsp != m->eng.nsp()) throw std::runtime_error("set_density_rows: species count differs from the model");
+  for (size_t i = 0; i < nrows * m->numX * nsp; ++i)
+    if (d[i] < 0) throw std::runtime_error("density must be non-negative (reference asserts density>=0, models/ecolab_model.cc:108)");
+  m->eng.set_density_rows((uint32_t)(y - m->y0), (uint32_t)nrows, d, nsp);
   ECO_CATCH
 }
 int eco_set_density_all_device(eco_model* m, const int32_t* d, size_t ncells, size_t nsp) {
@@ -727,6 +753,20 @@ int eco_step_host(eco_model* m, const int32_t* in, int32_t* out, size_t ncells, 
   if (!in || !out) throw std::runtime_error("step_host: null buffer");
   const uint64_t t = m->step_host(in, out, ncells, nsp, niter);
   if (total) *total = t / 2;   // :702
+  ECO_CATCH
+}
+int eco_step_async(eco_model* m, unsigned niter) {
+  ECO_TRY
+  need(m);
+  m->generate(niter);
+  m->migrate_local(false);
+  ECO_CATCH
+}
+int eco_migrate_wait(eco_model* m, uint64_t* total) {
+  ECO_TRY
+  need(m);
+  const uint64_t t = m->eng.migrate_result();
+  if (total) *total = t;
   ECO_CATCH
 }
 int eco_migrate_local(eco_model* m, uint64_t* total) {
@@ -834,7 +874,7 @@ int eco_species_totals(eco_model* m, int64_t* out, size_t nsp) {
 
 // ---- checkpoint / restart: self-describing little-endian dump -------------------------
 namespace {
-const char kMagic[8] = {'E', 'C', 'O', 'B', '2', '0', '0', 1};
+const char kMagic[8] = {'E', 'C', 'O', 'B', '2', '0', '0', 2};
 template <class T> void wr(FILE* f, const T& v) { if (fwrite(&v, sizeof v, 1, f) != 1) throw std::runtime_error("checkpoint: write failed"); }
 template <class T> void rd(FILE* f, T& v) { if (fread(&v, sizeof v, 1, f) != 1) throw std::runtime_error("restart: truncated file"); }
 template <class T> void wrv(FILE* f, const std::vector<T>& v) {
@@ -863,6 +903,9 @@ int eco_checkpoint(eco_model* m, const char* file) {
   wr(f, m->sp_sep); wr(f, m->mut_max); wr(f, m->repro_min); wr(f, m->repro_max); wr(f, m->odiag_min); wr(f, m->odiag_max); wr(f, m->gen_bias);
   wr(f, (uint8_t)m->fixMutation); wr(f, (uint8_t)m->fixMigration);
   wr(f, m->seed); wr(f, m->salt_t); wr(f, (int32_t)m->sp_cntr);
+  // the process-wide running-CLT gaussian generator (array_grand, src/random.cc:59-64) and the rank count that spaces the
+  // species labels (:462); libc rand() keeps its own state and is, as in the reference, not part of a checkpoint
+  wr(f, (uint32_t)m->nprocs); wr(f, g_grand.sum); wr(f, (uint32_t)g_grand.n);
   wrv(f, m->species); wrv(f, m->create); wrv(f, m->repro_rate); wrv(f, m->mutation); wrv(f, m->migration);
   wrv(f, m->diag); wrv(f, m->val); wrv(f, m->row); wrv(f, m->col);
   const size_t ns = m->eng.nsp();
@@ -889,10 +932,15 @@ int eco_restart(eco_model* m, const char* file) {
   int32_t spc;
   rd(f, m->seed); rd(f, m->salt_t); rd(f, spc);
   m->sp_cntr = spc;
+  uint32_t np, gn;
+  rd(f, np); rd(f, g_grand.sum); rd(f, gn);
+  m->nprocs = np; g_grand.n = gn;
   rdv(f, m->species); rdv(f, m->create); rdv(f, m->repro_rate); rdv(f, m->mutation); rdv(f, m->migration);
   rdv(f, m->diag); rdv(f, m->val); rdv(f, m->row); rdv(f, m->col);
   uint64_t ns; rd(f, ns);
   std::vector<int32_t> d; rdv(f, d);
+  for (int32_t v : d)
+    if (v < 0) throw std::runtime_error("restart: negative density in the checkpoint");
   if (pan) {
     m->panmictic = true; m->numX = m->numY = 1; m->y0 = 0; m->nyl = 1;
     m->eng.set_grid(1, 1, 0, 1, (uint32_t)ns);
@@ -915,22 +963,25 @@ int eco_halo_ptrs(eco_model* m, void** st, void** sb, void** rt, void** rb, size
   if (bytes) *bytes = m->eng.row_bytes();
   ECO_CATCH
 }
-int eco_ipc_export(eco_model* m, void* h, size_t* o1, size_t* o2) {
+int eco_peer_export(eco_model* m, void* blob, size_t blob_bytes) {
   ECO_TRY
   need(m);
-  m->eng.ipc_export(h, o1, o2);
+  static_assert(sizeof(eco::Engine::PeerBlob) <= ECO_PEER_BLOB_BYTES, "peer blob size");
+  if (blob_bytes < ECO_PEER_BLOB_BYTES) throw std::runtime_error("peer_export: blob buffer too small");
+  memset(blob, 0, ECO_PEER_BLOB_BYTES);
+  m->eng.peer_export(reinterpret_cast<eco::Engine::PeerBlob*>(blob));
   ECO_CATCH
 }
-int eco_ipc_import(eco_model* m, const void* h, void** base) {
+int eco_peer_connect(eco_model* m, const void* top_blob, const void* bottom_blob) {
   ECO_TRY
   need(m);
-  *base = m->eng.ipc_import(h);
+  m->eng.peer_connect(reinterpret_cast<const eco::Engine::PeerBlob*>(top_blob), reinterpret_cast<const eco::Engine::PeerBlob*>(bottom_blob));
   ECO_CATCH
 }
-int eco_set_peer_rows(eco_model* m, const void* top, const void* bottom) {
+int eco_peer_disconnect(eco_model* m) {
   ECO_TRY
   need(m);
-  m->eng.set_peer_rows(top, bottom);
+  m->eng.peer_disconnect();
   ECO_CATCH
 }
 int eco_alive_mask(eco_model* m, uint8_t* alive, size_t nsp) {
@@ -986,9 +1037,9 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   ECO_TRY
   need(m);
   const std::string k(knob);
-  if (k == "gen_threads") m->eng.gen_variant = value;
-  else if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
+  if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
   else if (k == "mig_variant") m->eng.mig_variant = value;
+  else if (k == "mig_stages") m->eng.mig_stages = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
   else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;
   else if (k == "gen_dual") m->eng.gen_dual = value;

@@ -9,9 +9,12 @@ Species parameters and beta are replicated.  Communication happens only where th
 reference communicates:
 
   migrate   halo rows (one grid row of densities per side) -- the reference's
-            prepareNeighbours (graphcode/prepare_neighbours.cc:17-72); either NCCL
-            send/recv into ghost rows or direct peer loads over NVLink (CUDA IPC),
-            plus a sum all-reduce of the migration total (:667-672)
+            prepareNeighbours (graphcode/prepare_neighbours.cc:17-72).  Default on
+            GPUs: the migrate kernel's boundary units read the neighbour ranks'
+            boundary rows directly out of their buffers over NVLink (CUDA IPC
+            mappings, device-side epoch counters, no collective; eco_peer_*);
+            fallback (ECOLAB_B200_HALO=nccl, or IPC unavailable): NCCL send/recv
+            into ghost rows.  Plus a sum all-reduce of the migration total (:667-672)
   condense  max all-reduce of the alive mask (MPI_LOR, :182-186)
   mutate    all-gather of the (cell, parent slot, count) records (:250), rank 0
             generates the new species' parameters and broadcasts only the appended
@@ -123,14 +126,17 @@ class Comm:
 #   ops.append_species(cells)              ops.migrate_local() -> sum|delta| (not halved)
 #   ops.halo_tensors() -> (send_up, recv_up, send_down, recv_down) or None; ops.halo_done()
 # ---------------------------------------------------------------------------------
-def dist_migrate(ops, comm):
-    """SpatialModel::migrate (models/ecolab_model.cc:616-703) on a row-slab partition."""
+def dist_migrate(ops, comm, wait=True):
+    """SpatialModel::migrate (models/ecolab_model.cc:616-703) on a row-slab partition.  wait=False (device path only):
+    nothing is read back; the caller fetches the total later with ops.last_migration()."""
     t = ops.halo_tensors()
     if t is not None:
         comm.sendrecv_rows(*t)
         ops.halo_done()
     dev_total = ops.migrate_local_device() if comm.backend == "nccl" and hasattr(ops, "migrate_local_device") else None
-    if dev_total is not None:   # all-reduce enqueued behind the kernel: one host synchronisation per migrate, at the end
+    if dev_total is not None:   # all-reduce enqueued behind the kernel: at most one host synchronisation per migrate, at the end
+        if not wait:
+            return None
         comm.dist.all_reduce(dev_total, op=comm.dist.ReduceOp.SUM, group=comm.group)
         return int(dev_total.cpu()[0]) // 2
     return comm.allreduce_sum(ops.migrate_local()) // 2   # :667-672, :702
@@ -169,6 +175,41 @@ class _DevMem:
                                          "version": 2}
 
 
+class _OwnedCell(_Cell):
+    """A cell of this rank's slab in a distributed run: reads are collective (see SpatialModel.cell)."""
+
+    def __init__(self, model, cid, j):
+        super().__init__(model, cid)
+        self.density = _Member(lambda: model._bcast_density(cid, j), lambda v: model._set_density(cid, v), name=f"cell[{cid}].density")
+
+    def nsp(self):
+        return sum(1 for v in self.density() if v != 0)
+
+
+class _RemoteCell:
+    """A cell owned by another rank: assignments are dropped (its owner executes the same statement), reads are
+    collective broadcasts from the owner."""
+
+    def __init__(self, model, cid, j):
+        self._m, self._id = model, cid
+
+        def _set(v):
+            a = np.asarray(list(v) if not isinstance(v, np.ndarray) else v)
+            if (a < 0).any():
+                raise EcolabError("density must be non-negative (reference asserts density>=0, models/ecolab_model.cc:108)")
+            model._note_remote_species(len(a))
+
+        self.density = _Member(lambda: model._bcast_density(cid, j), _set, name=f"cell[{cid}].density")
+        self.salt = _Member(lambda: model._salt(cid), name="salt")
+        self.id = _Member(lambda: cid, name="id")
+
+    def nsp(self):
+        return sum(1 for v in self.density() if v != 0)
+
+    def _list(self):
+        return ["density", "salt", "id"]
+
+
 class SpatialModel(EcolabModelBase):
     """spatial_ecolab.  Single process: the whole grid on one GPU.  Under torch.distributed
     (world > 1): this rank's row slab, with the exchanges described in the module docstring."""
@@ -181,6 +222,8 @@ class SpatialModel(EcolabModelBase):
         self._comm = comm
         self._nx = self._ny = 1
         self._y0, self._y1 = 0, 1
+        self._peer_version = None      # buf_version the neighbours' buffers were mapped for
+        self._peer_failed = False
 
     # ---- distribution ------------------------------------------------------------
     def attach(self, comm):
@@ -208,21 +251,84 @@ class SpatialModel(EcolabModelBase):
             self._y0, self._y1 = 0, ny
             check(self._L.eco_set_grid(self._h, nx, ny))
 
+    def restart(self, file):
+        """Model<M>::restart (include/ecolab.h:92-94); the grid geometry comes back with the file."""
+        super().restart(self._rank_file(file))
+        self._nx, self._ny = int(self._scalar("numX")), int(self._scalar("numY"))
+        self._y0 = int(self._scalar("y0"))
+        self._y1 = self._y0 + int(self._scalar("ny_local"))
+        self._peer_version = None
+
+    def checkpoint(self, file):
+        """One file per rank under torch.distributed (`file.rankN`): every rank holds its own slab."""
+        super().checkpoint(self._rank_file(file))
+
+    def _rank_file(self, file):
+        return f"{file}.rank{self.rank}" if self.world > 1 else str(file)
+
     def owns(self, i, j):
         return self._y0 <= j < self._y1
 
     def cell(self, i, j):
+        """EcolabCell of grid position (i, j).  Under torch.distributed every rank runs the same script, so the cell may
+        belong to another rank: assignments to it are then accepted and dropped (the owner performs the same
+        assignment), exactly as every MPI rank of the reference fills all cells before distributeObjects
+        (graphcode/graphcode.h:475-482); reading it fetches the density from its owner (a collective: all ranks must
+        make the same call, which an SPMD script does)."""
+        cid = int(i) + self._nx * int(j)
+        if self.world > 1 and not self.owns(i, j):
+            return _RemoteCell(self, cid, int(j))
+        if self.world > 1:
+            return _OwnedCell(self, cid, int(j))
+        return _Cell(self, cid)
+
+    def cell_local(self, i, j):
+        """The same for a cell this rank owns, without any collective (library code and tests; not the scripts' call)."""
         return _Cell(self, int(i) + self._nx * int(j))
 
-    def nsp(self):
-        """Living species per owned cell (SpatialModel::nsp, models/ecolab_model.cc:117-122)."""
+    def _owner_of_row(self, j):
+        for r in range(self.world):
+            y0, y1 = slab_bounds(self._ny, self.world, r)
+            if y0 <= j < y1:
+                return r
+        raise EcolabError("cell id outside the grid")
+
+    def _bcast_density(self, cid, j):
+        """Collective read of one cell's density from its owner."""
+        import torch
+        src = self._owner_of_row(j)
+        ns = int(self._scalar("nsp"))
+        a = np.asarray(self._get_density(cid), dtype=np.int32) if src == self.rank else np.zeros(ns, dtype=np.int32)
+        t = torch.from_numpy(a).to(self._comm.dev)
+        self._comm.dist.broadcast(t, src=src, group=self._comm.group)
+        return EcoList(t.cpu().numpy().tolist())
+
+    def nsp_local(self):
+        """Living species per OWNED cell (ascending cell id)."""
         nc = int(self._scalar("ncells_local"))
         a = np.empty(nc, dtype=np.uint32)
         if nc:
             check(self._L.eco_nsp_per_cell(self._h, _ptr(a), nc))
-        return EcoList(a.tolist())
+        return a
 
-    # graphcode operations that have nothing left to do under a static slab partition
+    def nsp(self):
+        """Living species per cell of the WHOLE grid, ascending cell id (SpatialModel::nsp, models/ecolab_model.cc:117-122:
+        the reference gathers the per-rank counts with MPI); an all-gather under torch.distributed."""
+        a = self.nsp_local()
+        if self.world == 1:
+            return EcoList(a.tolist())
+        import torch
+        sizes = [(slab_bounds(self._ny, self.world, r)[1] - slab_bounds(self._ny, self.world, r)[0]) * self._nx for r in range(self.world)]
+        mx = max(sizes)
+        pad = np.zeros(mx, dtype=np.int32)
+        pad[: len(a)] = a.astype(np.int32)
+        t = torch.from_numpy(pad).to(self._comm.dev)
+        outs = [torch.zeros_like(t) for _ in range(self.world)]
+        self._comm.dist.all_gather(outs, t, group=self._comm.group)
+        return EcoList(np.concatenate([o.cpu().numpy()[:n] for o, n in zip(outs, sizes)]).tolist())
+
+    # graphcode operations that have nothing left to do under a static slab partition: the partition is fixed by
+    # setGrid, objects never move
     def partitionObjects(self):
         return None
 
@@ -230,13 +336,81 @@ class SpatialModel(EcolabModelBase):
         return None
 
     def gather(self):
+        """Graph::gather (graphcode/gather.cc:17-38): afterwards rank 0 can read every cell.  Here every rank already
+        reads any cell through its owner (cell(i,j).density() is a collective broadcast), so gathering is a
+        synchronisation point: all kernels finished on every rank."""
         self.syncThreads()
+        if self.world > 1:
+            self._comm.dist.barrier(group=self._comm.group)
+
+    def density_rows(self, y, nrows):
+        """Whole grid rows [y, y+nrows) (all owned by this rank) as an int32 array [nrows*nx][nsp]."""
+        ns = int(self._scalar("nsp"))
+        a = np.empty((int(nrows) * self._nx, ns), dtype=np.int32)
+        if a.size:
+            check(self._L.eco_get_density_rows(self._h, int(y), int(nrows), _ptr(a), ns))
+        return a
+
+    def set_density_rows(self, y, a):
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        check(self._L.eco_set_density_rows(self._h, int(y), a.shape[0] // self._nx, _ptr(a), a.shape[1]))
+
+    # ---- halo over peer memory --------------------------------------------------------
+    def _peers_wanted(self):
+        import os
+        return (self.world > 1 and self._comm.backend == "nccl" and not self._peer_failed
+                and os.environ.get("ECOLAB_B200_HALO", "peer") != "nccl" and self._on_torch_stream())
+
+    def _ensure_peers(self):
+        """(Re)connect to the neighbour ranks' buffers when this rank's buffers were (re)allocated since the last
+        exchange.  Buffer versions move in lock-step on all ranks (same species counts everywhere), so every rank takes
+        this branch in the same migrate call; the exchange is a collective.  Returns True when the peer path is live."""
+        if not self._peers_wanted() or not int(self._scalar("nsp")):
+            return False
+        if self._peer_version == int(self._scalar("buf_version")) and int(self._scalar("peer_connected")):
+            return True
+        import torch
+        ok = 1
+        blob = np.zeros(256, dtype=np.uint8)
+        try:
+            check(self._L.eco_peer_export(self._h, _ptr(blob), blob.size))
+        except EcolabError:
+            ok = 0
+        t = torch.from_numpy(blob.copy()).to(self._comm.dev)
+        outs = [torch.zeros_like(t) for _ in range(self.world)]
+        self._comm.dist.all_gather(outs, t, group=self._comm.group)
+        blobs = [o.cpu().numpy() for o in outs]
+        if ok:
+            top = blobs[self.rank - 1] if self.rank > 0 else None
+            bot = blobs[self.rank + 1] if self.rank + 1 < self.world else None
+            try:
+                check(self._L.eco_peer_connect(self._h, _ptr(top) if top is not None else None, _ptr(bot) if bot is not None else None))
+            except EcolabError:
+                ok = 0
+        flag = torch.tensor([ok], device=self._comm.dev)
+        self._comm.dist.all_reduce(flag, op=self._comm.dist.ReduceOp.MIN, group=self._comm.group)   # all or nobody; also the barrier after connect
+        if int(flag.item()) == 0:
+            check(self._L.eco_peer_disconnect(self._h))
+            self._peer_failed = True      # IPC not available here: NCCL ghost rows from now on
+            return False
+        self._peer_version = int(self._scalar("buf_version"))
+        return True
+
+    def _note_remote_species(self, n):
+        """A density of n species was assigned to a cell of another rank: this rank's cells must have (at least) n
+        species rows too, as SpatialModel::makeConsistent takes the maximum over all cells (:725-735)."""
+        if n > int(self._scalar("nsp")) and self._y1 > self._y0:
+            first = self._y0 * self._nx
+            cur = np.asarray(self._get_density(first), dtype=np.int32)
+            self._set_density(first, np.concatenate([cur, np.zeros(n - len(cur), dtype=np.int32)]))
 
     # ---- per-rank halves over the C ABI ("ops" protocol) -------------------------------
     def halo_tensors(self):
         import torch
         if not int(self._scalar("nsp")):
             return None
+        if self._ensure_peers():
+            return None          # the kernel reads the neighbours' rows itself
         st, sb, rt, rb = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
         nb = C.c_size_t()
         check(self._L.eco_halo_ptrs(self._h, C.byref(st), C.byref(sb), C.byref(rt), C.byref(rb), C.byref(nb)))
@@ -279,6 +453,15 @@ class SpatialModel(EcolabModelBase):
         t = C.c_uint64()
         check(self._L.eco_migrate_local(self._h, C.byref(t)))
         return t.value
+
+    def last_migration(self):
+        """Total of the most recent migrate()/step(..., wait=False): blocks until it has finished (and, on a partitioned
+        grid, sums over the ranks)."""
+        t = C.c_uint64()
+        check(self._L.eco_migrate_wait(self._h, C.byref(t)))
+        if self.world == 1:
+            return t.value // 2
+        return self._comm.allreduce_sum(t.value) // 2
 
     def alive_mask(self):
         ns = int(self._scalar("nsp"))
@@ -328,21 +511,25 @@ class SpatialModel(EcolabModelBase):
         check(self._L.eco_append_species(self._h, _ptr(cells), len(cells)))
 
     # ---- the reflected methods ---------------------------------------------------------------
-    def migrate(self):
+    def migrate(self, wait=True):
         if self.world == 1:
             t = C.c_uint64()
             check(self._L.eco_migrate(self._h, C.byref(t)))
             return t.value
-        return dist_migrate(self, self._comm)
+        return dist_migrate(self, self._comm, wait)
 
-    def step(self, niter=1):
-        """generate(niter) then migrate(); returns migrate's total."""
+    def step(self, niter=1, wait=True):
+        """generate(niter) then migrate(); returns migrate's total.  wait=False enqueues both and returns None: no host
+        round trip per step (read the total of the last step with last_migration())."""
         if self.world == 1:
+            if not wait:
+                check(self._L.eco_step_async(self._h, int(niter)))
+                return None
             t = C.c_uint64()
             check(self._L.eco_step(self._h, int(niter), C.byref(t)))
             return t.value
         self.generate(niter)
-        return self.migrate()
+        return self.migrate(wait)
 
     def step_host(self, dens_in, dens_out, niter=1):
         """generate(niter) + migrate() on a HOST-resident state: `dens_in` [cell][nsp] int32 is uploaded, the result

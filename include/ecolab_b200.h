@@ -86,6 +86,9 @@ int eco_get_density(eco_model* m, size_t cell, int32_t* out, size_t cap, size_t*
 /* all owned cells, host buffer cell-major [cell][nsp] in ascending cell id */
 int eco_set_density_all(eco_model* m, const int32_t* d, size_t ncells, size_t nsp);
 int eco_get_density_all(eco_model* m, int32_t* out, size_t ncells, size_t nsp);
+/* a band of whole grid rows [y, y+nrows) (GLOBAL row index, all owned by this process), cell-major [cell][nsp] */
+int eco_get_density_rows(eco_model* m, size_t y, size_t nrows, int32_t* out, size_t nsp);
+int eco_set_density_rows(eco_model* m, size_t y, size_t nrows, const int32_t* d, size_t nsp);
 /* same with DEVICE buffers (device-resident pipelines, benchmarks) */
 int eco_set_density_all_device(eco_model* m, const int32_t* d_dev, size_t ncells, size_t nsp);
 int eco_get_density_all_device(eco_model* m, int32_t* out_dev, size_t ncells, size_t nsp);
@@ -108,6 +111,11 @@ int eco_migrate(eco_model* m, uint64_t* total);
 /* one driver-loop body of the spatial scripts (models/spatial_ecolab.py:67-69 minus mutate):
  * eco_generate(niter) followed by eco_migrate(total) as one call (fewer host round trips) */
 int eco_step(eco_model* m, unsigned niter, uint64_t* total);
+/* eco_step without the host round trip for migrate's return value: both kernels are enqueued on the model's stream and
+ * the call returns; eco_migrate_wait blocks until the last migrate has finished and returns its sum|delta| (NOT halved,
+ * owned cells only).  For throughput loops that read the total once at the end. */
+int eco_step_async(eco_model* m, unsigned niter);
+int eco_migrate_wait(eco_model* m, uint64_t* abs_delta_sum);
 /* the same body for a HOST-resident state: densities come from `in` and the result goes to `out` (both cell-major
  * [cell][nsp], ascending cell id, as eco_set/get_density_all; pinned memory makes the copies asynchronous).  Equivalent
  * to eco_set_density_all(in); eco_step(niter); eco_get_density_all(out) -- i.e. SpatialModel::generate :607-614 +
@@ -148,11 +156,17 @@ int eco_migrate_local_async(eco_model* m, void** total_dev);
 /* device pointers + byte size of the two boundary rows to send and the two ghost rows to fill */
 int eco_halo_ptrs(eco_model* m, void** send_top, void** send_bottom, void** recv_top, void** recv_bottom,
                   size_t* row_bytes);
-/* CUDA-IPC export of the current density buffer and import of a neighbour's;
- * peer rows, when set, replace the ghost rows in eco_migrate_local (P2P over NVLink). */
-int eco_ipc_export(eco_model* m, void* handle64, size_t* offset_first_row, size_t* offset_last_row);
-int eco_ipc_import(eco_model* m, const void* handle64, void** base_out);
-int eco_set_peer_rows(eco_model* m, const void* top_row, const void* bottom_row);
+/* Halo over peer memory instead of a ghost-row exchange (replaces graphcode's prepareNeighbours,
+ * graphcode/prepare_neighbours.cc:17-72, on NVLink): every rank exports an opaque blob (CUDA-IPC handles of its two
+ * density buffers and of its epoch counter + its slab geometry), the host language hands each rank the blobs of the ranks
+ * owning the rows above (lower y) and below its slab (NULL = none), and from then on eco_migrate_local's boundary units
+ * read the neighbours' boundary rows directly, ordered by device-side epoch counters (no collective, no host round trip).
+ * All ranks must then call migrate the same number of times.  A (re)allocation of the density buffers (scalar
+ * "buf_version" changes) disconnects; export and connect again. */
+#define ECO_PEER_BLOB_BYTES 256
+int eco_peer_export(eco_model* m, void* blob, size_t blob_bytes);
+int eco_peer_connect(eco_model* m, const void* top_blob, const void* bottom_blob);
+int eco_peer_disconnect(eco_model* m);
 /* condense halves: local alive mask (:173-179); apply a global mask (:188-194) */
 int eco_alive_mask(eco_model* m, uint8_t* alive, size_t nsp);
 int eco_condense_apply(eco_model* m, const uint8_t* alive, size_t nsp, unsigned* removed);
@@ -170,10 +184,11 @@ int eco_append_species(eco_model* m, const uint32_t* birth_cells, size_t n);
 void eco_array_urand_seed(int seed);
 void eco_array_grand_reset(void);
 
-/* tuning / profiling knobs (0 = automatic): "gen_threads" (consumer warps of generate(1): 12/16/20 with two blocks
- * per warp, 24/31 with one; threads/32 of the multi-step kernel), "gen_dual" (1 / -1: force two / one block per consumer
- * warp), "gen_stages", "gen_nobsmem", "mig_variant" (tiles a migrate warp spans: 1/2/4/8), "gen_dense", "dense_slices",
- * "timing" (1 = record a CUDA-event pair around every generate/migrate launch, 0 = off and reset) */
+/* tuning / profiling knobs (0 = automatic): "gen_dual" (-1: one species-row block per consumer warp of generate(1)),
+ * "gen_stages", "gen_nobsmem" (1: beta through L1/L2 even where it fits in shared memory), "mig_variant" (1 = register
+ * walker, 2 = tile-column pipeline), "mig_stages" (ring depth of the migrate pipeline), "gen_dense" (1 = tensor-core
+ * generate for dense beta; never automatic), "dense_slices", "timing" (1 = record a CUDA-event pair around every
+ * generate/migrate launch, 0 = off and reset) */
 int eco_set_tuning(eco_model* m, const char* knob, int value);
 /* device time per kernel kind since timing was switched on: out = {generate_ms, generate_launches,
  * migrate_ms, migrate_launches, ...}; *n = number of doubles available */

@@ -74,13 +74,20 @@ def test_sass_is_sm100a_with_bulk_copy(built):
     out = subprocess.run(["cuobjdump", "-sass", built], capture_output=True, text=True).stdout
     assert "sm_100a" in out
     assert "UBLKCP" in out          # cp.async.bulk (TMA unit) staging of the generate tiles
-    # no FP64 contraction in the reference-order arithmetic: bit-exactness vs the reference's x86-64 build.  The one
-    # kernel allowed to hold DFMA is the tensor-core path, whose Horner recombination of integer accumulators is exact
-    # either way (k_dense.cuh); everything else must be free of it.
+    # no FP64 contraction in the reference-order arithmetic: bit-exactness vs the reference's x86-64 build.  DFMA may
+    # appear in exactly two places: the tensor-core path, whose Horner recombination of integer accumulators is exact
+    # either way (k_dense.cuh), and the generate kernels' exact product fma(val, 2^52+n, -val*2^52) = fl(val*n)
+    # (k_generate.cuh, template flag FMA = true, the last template argument).  The FMA = false twins of the same source
+    # prove that nothing else in generate contracts; migrate, mutate, condense and the diagnostics hold none.
     funcs = out.split("Function : ")
     assert any("generate_dense_kernel" in f.split("\n", 1)[0] for f in funcs)
+    twins = 0
     for f in funcs[1:]:
         name = f.split("\n", 1)[0]
-        if "generate_dense_kernel" not in name:
+        fma_generate = re.search(r"generate_(pipe|multi)_kernelI.*Lb1EEEvNS", name) is not None
+        if re.search(r"generate_pipe_kernelI.*Lb0EEEvNS", name):
+            twins += 1
+        if "generate_dense_kernel" not in name and not fma_generate:
             assert "DFMA" not in f, name
+    assert twins >= 4
     assert "UTCIMMA" in out and "LDTM" in out     # tcgen05.mma kind::i8 and tcgen05.ld of the dense generate kernel

@@ -43,16 +43,30 @@ def test_generate_bit_exact(oracle_mod, gpu, grid, nsp, k):
 
 @pytest.mark.parametrize("grid,nsp,k", [((8, 5), 37, 3), ((33, 3), 64, 5), ((70, 9), 129, 3), ((17, 4), 1000, 3), ((5, 3), 8, 1),
                                         ((9, 2), 200, 0)])
-@pytest.mark.parametrize("warps", [0, 12])
-def test_generate_dual_block_consumers(oracle_mod, gpu, grid, nsp, k, warps):
-    """generate(1) with two species-row blocks per consumer warp (knob gen_dual): same bits, odd block counts included."""
+@pytest.mark.parametrize("knob,val", [("gen_dual", -1), ("gen_nobsmem", 1), ("gen_stages", 1)])
+def test_generate_kernel_forms(oracle_mod, gpu, grid, nsp, k, knob, val):
+    """generate(1) through each shipped form of the pipeline kernel (one species-row block per consumer warp instead of
+    two, beta through L1/L2 instead of shared memory, a single tile buffer): same bits, odd block counts included."""
     o, m, grid = pair(oracle_mod, gpu, grid, nsp, k)
-    m.set_tuning("gen_dual", 1)
-    if warps:
-        m.set_tuning("gen_threads", warps)
-    for _ in range(3):
-        o.generate(1); m.generate(1)
+    m.set_tuning(knob, val)
+    for niter in (1, 1, 2):
+        o.generate(niter); m.generate(niter)
         assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
+
+
+def test_generate_beta_values_outside_the_exact_fma_range(oracle_mod, gpu):
+    """The product val*n is one fused multiply-add against -(val*2^52) (k_generate.cuh); that needs val = 0 or a normal
+    number.  Subnormal and huge entries switch the engine to the multiply-then-add kernel: same bits either way."""
+    grid, nsp = (9, 4), 40
+    p = synth(nsp, 4, 13)
+    p["interaction.val"][::7] = 5e-324          # smallest subnormal
+    p["interaction.val"][3::11] = -2.5e-310
+    p["interaction.val"][5::13] = 0.0
+    d = densities(36, nsp, 13)
+    o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
+    for niter in (1, 3):
+        o.generate(niter); m.generate(niter)
+        assert np.array_equal(m.density_array(), o.get_density_all())
 
 
 @pytest.mark.parametrize("grid,nsp,k", [(None, 100, 3), ((8, 5), 37, 3), ((33, 3), 64, 16)])
@@ -96,13 +110,17 @@ def test_migrate_bit_exact_and_conserves(oracle_mod, gpu, grid, nsp, k):
         assert m.last_mig_tstep() == m.tstep()
 
 
-@pytest.mark.parametrize("grid,nsp,k", [((250, 3), 1000, 3), ((256, 4), 37, 3), ((120, 5), 300, 2), ((64, 7), 2000, 1)])
-@pytest.mark.parametrize("span", [2, 4, 8])
-def test_migrate_warp_spans(oracle_mod, gpu, grid, nsp, k, span):
-    """migrate with a warp spanning 2/4/8 adjacent tiles (knob mig_variant; the engine falls back to the widest span
-    the tile count allows): same bits, ragged last tiles included."""
+@pytest.mark.parametrize("grid,nsp,k", [((250, 3), 1000, 3), ((256, 4), 37, 3), ((120, 5), 300, 2), ((64, 7), 2000, 1), ((40, 70), 1000, 3),
+                                        ((33, 150), 64, 2), ((7, 41), 2100, 1)])
+@pytest.mark.parametrize("variant,stages", [(1, 0), (2, 2), (2, 5), (2, 12)])
+def test_migrate_kernels(oracle_mod, gpu, grid, nsp, k, variant, stages):
+    """migrate through the register walker (variant 1) and the tile-column pipeline (variant 2) at several ring depths:
+    same bits, ragged last tiles, partial species groups, many rows per unit and tile widths 32/16/8/4 included
+    (2100 species = 4-cell tiles: only the walker exists there and the knob falls back to it)."""
     o, m, grid = pair(oracle_mod, gpu, grid, nsp, k, mig=0.11)
-    m.set_tuning("mig_variant", span)
+    m.set_tuning("mig_variant", variant)
+    if stages:
+        m.set_tuning("mig_stages", stages)
     for it in range(2):
         o.generate(1); m.generate(1)
         assert m.migrate() == o.migrate()
@@ -122,8 +140,8 @@ def test_migrate_extreme_densities(oracle_mod, gpu):
     d[rng.random(d.shape) < 0.1] = 2 ** 31 - 2
     o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
     o.set("tstep", 1); m.tstep(1)            # dt = 1 since last_mig_tstep = 0
-    for span in (0, 2, 4):
-        m.set_tuning("mig_variant", span)
+    for variant in (0, 1, 2):
+        m.set_tuning("mig_variant", variant)
         before = m.species_totals()
         assert m.migrate() == o.migrate()
         got = m.density_array()

@@ -48,8 +48,6 @@ def main():
     nx = ny = args.n
     m.setGrid(nx, ny)
     m.seed(10)
-    if args.gen_warps:
-        m.set_tuning("gen_threads", args.gen_warps)
     m.fill_density_random(0, 199)
     elems = nx * ny * args.nsp
     out = {"workload": f"spatial {nx}x{ny} cells x {args.nsp} species, {args.nnz} nnz/row", "hbm_peak_gbs": peak, "passes": {}}
