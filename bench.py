@@ -92,11 +92,21 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU leg (oracle): the reference's algorithm on the host cores.  Only place bench.py touches oracle/.
 # ------------------------------------------------------------------------------------------------
+def host_threads():
+    """Every host thread this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is rank 0
+    alone on the box, so it takes the affinity mask, not that variable."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_leg(nsp, nnz, steps, warmup, budget_s=20.0):
+    threads = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(threads)     # before libgomp initialises
     from oracle import oracle as O
     from helpers import SCALARS, load_oracle
     O.build()
-    threads = O.max_threads()
     O.set_threads(threads)
     p = synth_params(nsp, nnz)
     # bounded sample of the same workload: a 256 x H strip of the grid, H sized so the whole leg takes ~budget_s
@@ -216,12 +226,12 @@ def run_native(args):
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    moved = 0
     for _ in range(args.steps):
-        moved = m.step(1)
+        m.step(1, wait=False)       # no host round trip per step: migrate's total is read once, after the loop
     e1.record(stream)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    moved = m.last_migration()
     ms = e0.elapsed_time(e1)
     launches = m.launches() - l0
     kt = m.kernel_times()
@@ -258,6 +268,11 @@ def run_native(args):
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]},
                 "step_frac_at_16B": (16.0 * updates_per_step / world * args.steps / (ms * 1e-3) / 1e9) / peak}
 
+    # ---- verify (outside the timed region): partition-independent fingerprints of the state + band parity vs the oracle ----
+    verify = None
+    if not args.no_verify:
+        verify = verify_leg(m, args, nx, ny, world, rank)
+
     del m   # frees the device buffers before the next leg allocates its own
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region, bounded grid ----
     e2e = None
@@ -275,27 +290,141 @@ def run_native(args):
                 "config": {"workload": workload_name(nx, ny, args.nsp),
                            "nnz_per_row": args.nnz, "partition": f"{world} row slab(s)", "l2": "inputs (%.1f GiB) larger than L2" % (updates_per_step * 4 / 2**30),
                            "rng": "Philox4x32-10 keyed (seed, cell, slot, tstep)", "migrated_last_step": int(moved)},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "verify": verify}
+        extra = {}
+        if world == 1 and not args.no_extra:
+            extra = extra_legs(E, args, local, stream)
+        line["extra"] = extra
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def e2e_leg(E, args, comm, local, stream, world, rank):
-    """set_density_all(host) -> step(1) -> get_density_all(host): the call sequence of a host-resident user
-    (what the reference's Python getters/setters do), pinned host buffers, copies inside the timed region."""
+def verify_leg(m, args, nx, ny, world, rank):
+    """Two more steps, each checked on a 4-row band against the oracle fed with the GPU's own pre-step rows (top of the
+    grid; the middle, where every even partition has a seam), then fingerprints of the state that do not depend on the
+    partition: the driver can compare the lines of N = 1/2/4/8.  The oracle is the checker here, never the thing timed."""
+    import hashlib
     import torch
     import torch.distributed as dist
-    nx = ny = args.e2e_n
+    from oracle import oracle as O
+    from helpers import SCALARS, band_step_equals_oracle, collect_rows
+    if rank == 0:
+        O.build()
+    p = synth_params(args.nsp, args.nnz)
+    bands = [0, max(0, ny // 2 - 2)]
+    nb = min(4, ny)
+    ok = []
+    for y in bands:
+        eq, _ = band_step_equals_oracle(O, m, p, SCALARS, 10, y, nb)
+        ok.append(eq)
+    tot = torch.from_numpy(m.species_totals()).cuda()
+    if world > 1:
+        dist.all_reduce(tot)
+    rows = [collect_rows(m, y, nb) for y in bands]
+    if rank != 0:
+        return None
+    h = lambda a: hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]   # noqa: E731
+    return {"tstep": int(m.tstep()), "band_rows": [[y, y + nb] for y in bands], "band_equal_oracle": bool(all(ok)),
+            "band_sha1": [h(r) for r in rows], "species_totals_sha1": h(tot.cpu().numpy()),
+            "individuals": int(tot.sum().item()),
+            "note": "after warmup+steps+2 steps; bands checked against the CPU oracle run on the GPU's own pre-step rows"}
+
+
+def extra_legs(E, args, local, stream):
+    """SURVEY 8(d) legs beside the headline (N = 1 only, each bounded to a few seconds): the nnz/row sweep of generate on
+    C3, the scripts' real cadence generate(100)+mutate()+migrate()+condense() on C2 with the scripts' parameters (this is
+    the leg that times the host-serial ModelData::mutate/condense stage), and the dense config 5 on the tensor cores."""
+    import copy
+    import torch
+    out = {}
+    sweep = {}
+    for nnz in (3, 16, 51):
+        a = copy.copy(args); a.nnz = nnz
+        m = build_model(E, a, 1024, 1024, None, local, stream)
+        for _ in range(3):
+            m.step(1, wait=False)
+        m.set_tuning("timing", 1)
+        torch.cuda.synchronize()
+        for _ in range(5):
+            m.step(1, wait=False)
+        torch.cuda.synchronize()
+        kt = m.kernel_times()
+        m.set_tuning("timing", 0)
+        g, mg = kt["generate"][0] / 5, kt["migrate"][0] / 5
+        sweep[str(nnz)] = {"generate_ms": g, "migrate_ms": mg, "updates_per_s": 2 ** 30 / ((g + mg) * 1e-3),
+                           "generate_hbm_frac": 8.0 * 2 ** 30 / (g * 1e-3) / 1e9 / peaks()[0]}
+        del m
+    out["nnz_sweep_c3"] = {"workload": "spatial 1024x1024 cells x 1024 species, generate(1)+migrate(), 5 steps", "by_nnz_per_row": sweep}
+    # the scripts' cadence (models/spatial_ecolab.py:66-78) at BASELINE.json config 2's shape
+    a = copy.copy(args); a.nsp = 1000; a.nnz = 3
+    m = build_model(E, a, 64, 64, None, local, stream)
+    m.mut_max(1e-5); m.mutation(np.full(1000, 1e-5))
+    E.lib().eco_array_urand_seed(10)
+    rounds, walls, dev = 4, [], []
+    for r in range(rounds):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream); m.generate(100); e1.record(stream)
+        m.mutate(); m.migrate(); m.condense()
+        torch.cuda.synchronize()
+        walls.append(time.perf_counter() - t0); dev.append(e0.elapsed_time(e1) * 1e-3)
+    upd = 64 * 64 * 1000 * 100
+    out["cadence_c2"] = {"workload": "spatial 64x64 cells x 1000 species (3 nnz/row, mutation = mut_max = 1e-5, the scripts' parameters): "
+                                     "generate(100)+mutate()+migrate()+condense() per round",
+                         "rounds": rounds, "wall_ms_per_round": [w * 1e3 for w in walls], "generate100_ms_per_round": [d * 1e3 for d in dev],
+                         "species_after": len(m.species),
+                         "generation_updates_per_s": upd / float(np.median(walls)),
+                         "non_generate_share": 1.0 - float(np.median(dev)) / float(np.median(walls))}
+    del m
+    if not args.no_dense:
+        try:
+            out["dense_c5"] = dense_leg(E, args, local, stream, steps=3, warmup=2)
+        except Exception as ex:   # noqa: BLE001
+            out["dense_c5"] = {"unavailable": str(ex)[:200]}
+    return out
+
+
+def e2e_grid(args, world):
+    """The grid of the e2e leg: the metric's own (C4) when its host copy, split over the ranks, stays within 32 GiB of
+    pinned memory per rank and 35 % of the box's available RAM in total; else the largest square power-of-two grid that does."""
+    if args.e2e_n:
+        return args.e2e_n
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:   # noqa: BLE001
+        avail = 64 << 30
+    n = 4096
+    while n > 256:
+        total = 2 * n * n * args.nsp * 4          # in + out
+        if total / world <= (32 << 30) and total <= 0.35 * avail:
+            break
+        n //= 2
+    return n
+
+
+def e2e_leg(E, args, comm, local, stream, world, rank):
+    """The step through the host-buffer API: pinned HOST densities in, pinned HOST densities out, H2D + kernels + D2H
+    inside the timed region (what a host-resident user of the reference's getters/setters pays).  eco_step_host streams
+    bands of grid rows; under torch.distributed every rank streams its own slab over its own PCIe link."""
+    import torch
+    import torch.distributed as dist
+    nx = ny = e2e_grid(args, world)
     m = build_model(E, args, nx, ny, comm, local, stream)
     nloc = (m._y1 - m._y0) * nx
-    host_in = torch.randint(0, 200, (nloc, args.nsp), dtype=torch.int32).pin_memory()
-    host_out = torch.empty((nloc, args.nsp), dtype=torch.int32).pin_memory()
+    host_in = torch.empty((nloc, args.nsp), dtype=torch.int32, pin_memory=True)
+    host_out = torch.empty((nloc, args.nsp), dtype=torch.int32, pin_memory=True)
     a_in, a_out = host_in.numpy(), host_out.numpy()
+    block = np.random.default_rng(5 + rank).integers(0, 200, size=(min(nloc, 16384), args.nsp), dtype=np.int32)
+    for i in range(0, nloc, len(block)):          # synthetic state, mean 100, tiled from one random block
+        a_in[i:i + len(block)] = block[: min(len(block), nloc - i)]
     import ctypes as C
 
     def one():
-        if world == 1 and not args.e2e_unpipelined:
+        if not args.e2e_unpipelined:
             return m.step_host(a_in, a_out, 1)     # eco_step_host: banded H2D / kernels / D2H pipeline
         E._cabi.check(m._L.eco_set_density_all(m._h, C.c_void_p(a_in.ctypes.data), nloc, args.nsp))
         moved = m.step(1)
@@ -307,7 +436,7 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    steps = max(2, min(args.steps, 5))
+    steps = max(2, min(args.steps, 4))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(steps):
@@ -319,29 +448,24 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    assert int(a_out.sum()) > 0
+    assert int(a_out[:1024].sum()) > 0
     val = nx * ny * args.nsp * steps / (ms * 1e-3)
     del m
-    return {"value": val, "unit": UNIT, "h2d_bytes_per_step": int(nx * ny * args.nsp * 4), "d2h_bytes_per_step": int(nx * ny * args.nsp * 4 + 8),
-            "workload": f"spatial {nx}x{ny} cells x {args.nsp} species through host buffers (bounded: pinned host copy of the full "
-                        f"grid per step)", "steps": steps, "ms_per_step": ms / steps,
-            "call": "eco_step_host (row-banded H2D/kernel/D2H pipeline)" if world == 1 and not args.e2e_unpipelined
-                    else "eco_set_density_all + eco_step + eco_get_density_all"}
+    return {"value": val, "unit": UNIT, "h2d_bytes_per_step": int(nx * ny * args.nsp * 4), "d2h_bytes_per_step": int(nx * ny * args.nsp * 4 + 8 * world),
+            "workload": f"spatial {nx}x{ny} cells x {args.nsp} species through pinned host buffers, {world} row slab(s), "
+                        f"{nloc * args.nsp * 4 / 2**30:.1f} GiB per rank each way per step", "steps": steps, "ms_per_step": ms / steps,
+            "call": "eco_step_host (row-banded H2D/kernel/D2H pipeline; partitioned: eco_step_host_begin + halo + eco_step_host)"
+                    if not args.e2e_unpipelined else "eco_set_density_all + eco_step + eco_get_density_all"}
 
 
-def run_dense(args):
+def dense_leg(E, args, local, stream, steps, warmup, sparse_too=False):
     """BASELINE.json config 5: 256 x 256 cells x 8192 species, beta fully dense -- generate on the tensor cores
-    (tcgen05 kind::i8 slices, ecolab_b200/csrc/k_dense.cuh) + migrate, and the FP64 sparse kernel on the same model."""
+    (tcgen05 kind::i8 slices, ecolab_b200/csrc/k_dense.cuh) + migrate; optionally the FP64 sparse kernel on the same model."""
     import torch
-    import ecolab_b200 as E
-    import ctypes as C
     from helpers import SCALARS
-    torch.cuda.set_device(0)
-    stream = torch.cuda.Stream()
-    torch.cuda.set_stream(stream)
-    nx, ny, nsp = args.nx or 256, args.ny or 256, args.nsp if args.nsp != 1024 else 8192
+    nx, ny, nsp = args.dense_n, args.dense_n, args.dense_nsp
     rng = np.random.default_rng(10)
-    m = E.SpatialModel(0, None)
+    m = E.SpatialModel(local, None)
     m.set_stream(stream)
     for k, v in SCALARS.items():
         getattr(m, k)(v)
@@ -365,17 +489,17 @@ def run_dense(args):
     updates = nx * ny * nsp
     if args.dense_prof:
         m._scalar("dense_prof0")     # enables the in-kernel cycle counters
-    for _ in range(args.warmup):
-        m.step(1)
+    for _ in range(warmup):
+        m.step(1, wait=False)
     assert m._scalar("dense_active") == 1
     m.set_tuning("timing", 1)
     torch.cuda.synchronize()
     l0 = m.launches()
-    sampler = ClockSampler(0); sampler.start()
+    sampler = ClockSampler(local); sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    for _ in range(args.steps):
-        m.step(1)
+    for _ in range(steps):
+        m.step(1, wait=False)
     e1.record(stream)
     torch.cuda.synchronize()
     clocks = sampler.stop()
@@ -387,18 +511,20 @@ def run_dense(args):
     mma_ms = kt["dense_mma"][0] / max(kt["dense_mma"][1], 1)
     pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     bf16 = float(pk.get("bf16_tflops_sustained", 1400.0))
-    peak = 2.0 * bf16      # int8 tensor rate = 2 x bf16 (nominal 4.5 vs 2.25 POP/s); measured bf16 sustained x 2
-    launches_per_step = kt["dense_mma"][1] / args.steps
+    launches_per_step = kt["dense_mma"][1] / steps
     achieved = 2.0 * macs / (mma_ms * launches_per_step * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "kernel": "generate_dense_kernel", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)",
-                "frac": achieved / peak, "traffic": None,
-                "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops_sustained (int8 = 2 x bf16 rate; of measured)" if pk else "fallback",
-                "executed_int8_macs_per_step": macs, "beta_slices": int(args.dense_slices or 3), "density_slices": q,
-                "algorithmic_tflops": 2.0 * nsp * updates / (mma_ms * launches_per_step * 1e-3) / 1e12,
-                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]}}
-    # the FP64 sparse kernel on the same dense model (config 5: "tcgen05 contraction path vs sparse path")
+    alg = 2.0 * nsp * updates / (mma_ms * launches_per_step * 1e-3) / 1e12
+    # No measured int8 tensor peak exists in MEASURED_PEAKS.json (the driver measures bf16 only), so the roofline is quoted
+    # on the ALGORITHMIC rate -- 2*nsp flops per update, what a bf16 GEMM of the same shape would be credited -- against
+    # the measured bf16 peak; the executed int8 rate (P*Q slices) is reported beside it without a fraction.
+    roofline = {"bound": "tensor", "kernel": "generate_dense_kernel", "achieved": alg, "peak": bf16, "unit": "TFLOP/s",
+                "frac": alg / bf16, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured); achieved = algorithmic 2*nsp flops per update" if pk else "fallback",
+                "executed_int8_tops": achieved, "executed_int8_macs_per_step": macs,
+                "beta_slices": int(args.dense_slices or 3), "density_slices": q,
+                "kernels_ms_per_step": {k: v[0] / steps for k, v in kt.items() if v[1]}}
     sparse_ms = None
-    if not args.no_cpu:
+    if sparse_too:   # the FP64 sparse kernel on the same dense model (config 5: "tcgen05 contraction path vs sparse path")
         try:
             m.set_tuning("gen_dense", -1)
             m.generate(1)
@@ -412,14 +538,23 @@ def run_dense(args):
     if args.dense_prof:
         names = ("mma_wait_tmem_empty", "mma_wait_smem_full", "mma_issue", "tiles", "epi_wait_tmem_full", "epi_work")
         roofline["cta0_cycles_last_launch"] = {n: int(m._scalar(f"dense_prof{i}")) for i, n in enumerate(names)}
-    line = {"metric": METRIC, "value": updates * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+    del m
+    return {"metric": METRIC, "value": updates * steps / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "s8 x u8 -> s32 slices, f64 epilogue -> i32", "data": "synthetic",
             "config": {"workload": f"dense-interaction stress: spatial {nx}x{ny} cells x {nsp} species, beta fully dense, generate(1)+migrate() per step",
                        "l2": "inputs (%.1f GiB) larger than L2" % (updates * 4 / 2**30)},
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline,
-            "sparse_fp64_generate_ms": sparse_ms, "dense_generate_ms": (kt["dense_mma"][0] + kt["dense_pack"][0]) / args.steps}
-    print(json.dumps(line))
+            "sparse_fp64_generate_ms": sparse_ms, "dense_generate_ms": (kt["dense_mma"][0] + kt["dense_pack"][0]) / steps}
+
+
+def run_dense(args):
+    import torch
+    import ecolab_b200 as E
+    torch.cuda.set_device(0)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    print(json.dumps(dense_leg(E, args, 0, stream, args.steps, args.warmup, sparse_too=not args.no_cpu)))
 
 
 def main():
@@ -432,7 +567,7 @@ def main():
     ap.add_argument("--ny", type=int, default=0)
     ap.add_argument("--nsp", type=int, default=1024)
     ap.add_argument("--nnz", type=int, default=3)
-    ap.add_argument("--e2e-n", type=int, default=1024, dest="e2e_n")
+    ap.add_argument("--e2e-n", type=int, default=0, dest="e2e_n", help="grid edge of the e2e leg (0 = the metric's grid where the host copy fits)")
     ap.add_argument("--mig-stages", type=int, default=0, dest="mig_stages")
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
     ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
@@ -441,10 +576,15 @@ def main():
     ap.add_argument("--e2e-unpipelined", action="store_true", dest="e2e_unpipelined")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-verify", action="store_true", dest="no_verify")
+    ap.add_argument("--no-extra", action="store_true", dest="no_extra")
+    ap.add_argument("--no-dense", action="store_true", dest="no_dense")
     ap.add_argument("--dense", action="store_true", help="config 5: 256x256x8192, dense beta, tensor-core generate")
     ap.add_argument("--dense-slices", type=int, default=0, dest="dense_slices")
     ap.add_argument("--dense-prof", action="store_true", dest="dense_prof")
     ap.add_argument("--dense-dmax", type=int, default=199, dest="dense_dmax")
+    ap.add_argument("--dense-n", type=int, default=256, dest="dense_n")
+    ap.add_argument("--dense-nsp", type=int, default=8192, dest="dense_nsp")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: native libraries that write to file descriptor 1 (NCCL prints its version
     # there) are diverted to stderr, Python's own stdout keeps the original descriptor

@@ -59,6 +59,7 @@ SIGNATURES = {
     "eco_step": [_vp, C.c_uint, _P(_u64)],
     "eco_step_async": [_vp, C.c_uint],
     "eco_migrate_wait": [_vp, _P(_u64)],
+    "eco_step_host_begin": [_vp, _vp, _sz, _sz, C.c_uint],
     "eco_step_host": [_vp, _vp, _vp, _sz, _sz, C.c_uint, _P(_u64)],
     "eco_condense": [_vp, _P(C.c_uint)],
     "eco_mutate": [_vp],

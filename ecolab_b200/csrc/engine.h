@@ -77,7 +77,10 @@ class Engine {
   uint64_t migrate_result();   // blocks on the async total of the last migrate
   // generate(niter) + migrate with HOST cell-major buffers [cell][nsp] in and out, streamed in bands of grid rows:
   // H2D of band k+1, the kernels of band k and D2H of band k-1 overlap (full-duplex PCIe); returns sum |delta|
-  uint64_t step_host(const int32_t* in_host, int32_t* out_host, uint32_t niter, uint64_t t0, uint32_t seed, const double* cm_host);
+  uint64_t step_host(const int32_t* in_host, int32_t* out_host, uint32_t niter, uint64_t t0, uint32_t seed, const double* cm_host,
+                     bool boundary_done = false);
+  // partitioned grids: upload + generate the slab's first and last row ahead of the halo exchange (see engine_ops.inc)
+  void step_host_begin(const int32_t* in_host, uint32_t niter, uint64_t t0, uint32_t seed);
   // alive[s] = 1 iff some owned cell has density != 0
   void alive_mask(uint8_t* alive_host);
   // compact species rows: keep[s] != 0 survives, order preserved
@@ -205,6 +208,7 @@ class Engine {
   unsigned long long* d_total_ = nullptr;              // migrate total / counters
   unsigned long long* h_total_ = nullptr;              // pinned
   MutRecord* d_rec_ = nullptr; size_t rec_cap_ = 0;
+  uint32_t* d_scan_ = nullptr; size_t scan_cap_ = 0;   // mutate: per-cell event counts + scan block totals
   int32_t* d_stage_ = nullptr; size_t stage_cap_ = 0;  // cell-major staging
   int32_t* d_band_[4] = {nullptr, nullptr, nullptr, nullptr}; size_t band_cap_ = 0;   // step_host: 2 in + 2 out band stagings
   void* st_in_ = nullptr; void* st_out_ = nullptr;       // copy streams of step_host

@@ -250,7 +250,7 @@ __device__ __forceinline__ void mig_wait_flag(const unsigned int* flag, unsigned
     unsigned int v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
     if ((int)(v - epoch) >= 0) return;
-    if (clock64() - t0 > 4000000000ll) { atomicExch(err, 1u); return; }   // ~2 s
+    if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); return; }   // ~10 s
     __nanosleep(200);
   }
 }

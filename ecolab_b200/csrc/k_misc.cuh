@@ -72,51 +72,182 @@ __global__ void __launch_bounds__(256) compact_kernel(int32_t* buf, size_t tile_
 
 // ---------------------------------------------------------------------------------------------
 // mutate, cell side (reference EcolabPoint::mutate, models/ecolab_model.cc:278-314):
-//   k = ROUND(ms[s] * n[c][s]) with the stage-1 Philox stream; n -= k; record (cell, slot, k>0)
+//   k = ROUND(ms[s] * n[c][s]) with the stage-1 Philox stream; n -= k; record (cell, slot, k) for k > 0
+// The reference concatenates the per-cell lists in cell order and, inside a cell, in slot order (gen_index,
+// include/arrays.h:2477-2486; its device build does this with joint_exclusive_scan, :284-306).  Here: two passes over
+// the densities with a scan between them, no global atomics, no sort --
+//   mutate_count_kernel   per-cell event counts (the draws are counter-based, so pass 2 can recompute them)
+//   scan_*_kernel         exclusive prefix sum over the owned cells in cell-id order -> first record of every cell
+//   mutate_emit_kernel    recomputes the draws, ranks the events of a cell by slot (warp ballots + a per-tile running
+//                         base in shared memory), writes each record at its final position and subtracts the mutants
 // ---------------------------------------------------------------------------------------------
 struct MutRec { uint32_t cell, slot, count; };
 
-__global__ void __launch_bounds__(256) mutate_scan_kernel(const Layout L, const double* ms, uint32_t seed,
-                                                          unsigned long long t, MutRec* rec, unsigned long long rec_cap,
-                                                          unsigned long long* count) {
+// born counts of this thread's 4 cells of species row s (0 where nothing happens)
+__device__ __forceinline__ void mutate_born(const Layout& L, const int4 v, double m, uint32_t xq, uint32_t yg, uint32_t s,
+                                            unsigned long long t, uint32_t seed, int (&born)[4]) {
+  born[0] = born[1] = born[2] = born[3] = 0;
+  if ((v.x | v.y | v.z | v.w) == 0 || !(m > 0.0)) return;   // extinct here / ROUND(x <= 0) = 0 without a draw
+  const uint4 u = draw4(xq, yg, s, t, seed, 1u);
+  const int n[4] = {v.x, v.y, v.z, v.w};
+  const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (n[k] > 0 && xq * 4 + k < L.nx) born[k] = round_stoch(__dmul_rn(m, u2d((uint32_t)n[k])), uu[k]);
+}
+
+// pass 1: counts[yl*nx + x] = number of species slots of that cell with born > 0.  One CTA per tile at a time.
+__global__ void __launch_bounds__(256) mutate_count_kernel(const Layout L, const double* __restrict__ ms, uint32_t seed,
+                                                           unsigned long long t, uint32_t* __restrict__ counts) {
+  __shared__ uint32_t cnt[32];
   const uint32_t ntiles = L.ntx * L.ny, qpr = L.tw / 4, per = L.nsp * qpr;
   for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    int4* tp = reinterpret_cast<int4*>(L.base + (size_t)tile * L.tile_stride);
+    if (threadIdx.x < 32) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int4* tp = reinterpret_cast<const int4*>(L.base + (size_t)tile * L.tile_stride);
     const uint32_t yl = tile / L.ntx, tx = tile - yl * L.ntx, yg = L.y0 + yl;
+    uint32_t c[4] = {0, 0, 0, 0};
+    const uint32_t qd = threadIdx.x % qpr;      // blockDim is a multiple of qpr: a thread always sees the same 4 cell columns
     for (uint32_t i = threadIdx.x; i < per; i += blockDim.x) {
-      const uint32_t s = i / qpr, qd = i - s * qpr;
-      int4 v = tp[i];
-      if ((v.x | v.y | v.z | v.w) == 0) continue;   // densities are non-negative: all four extinct here
-      const double m = __ldg(ms + s);
-      if (!(m > 0.0)) continue;                     // ROUND(x <= 0) = 0 without a draw
-      const uint32_t xq = tx * qpr + qd;
-      const uint4 u = draw4(xq, yg, s, t, seed, 1u);
-      int n[4] = {v.x, v.y, v.z, v.w};
-      const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
-      bool any = false;
+      const uint32_t s = i / qpr;
+      int born[4];
+      mutate_born(L, tp[i], __ldg(ms + s), tx * qpr + qd, yg, s, t, seed, born);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const uint32_t x = xq * 4 + k;
-        if (n[k] > 0 && x < L.nx) {
-          const int born = round_stoch(__dmul_rn(m, u2d((uint32_t)n[k])), uu[k]);
-          if (born > 0) {
-            const unsigned long long slot = atomicAdd(count, 1ull);
-            if (slot < rec_cap) { rec[slot] = MutRec{yg * L.nx + x, s, (uint32_t)born}; n[k] -= born; any = true; }
-          }
-        }
-      }
-      if (any) tp[i] = make_int4(n[0], n[1], n[2], n[3]);
+      for (int k = 0; k < 4; ++k) c[k] += born[k] > 0;
     }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (c[k]) atomicAdd(&cnt[4 * qd + k], c[k]);   // shared-memory atomics only
+    __syncthreads();
+    const uint32_t x = tx * L.tw + threadIdx.x;
+    if (threadIdx.x < L.tw && x < L.nx) counts[(size_t)yl * L.nx + x] = cnt[threadIdx.x];
+    __syncthreads();
   }
 }
 
-// undo a scan whose record buffer overflowed (the scan is then repeated with a larger buffer)
-__global__ void mutate_undo_kernel(const Layout L, const MutRec* rec, uint32_t nrec) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nrec) return;
-  const MutRec r = rec[i];
-  const uint32_t yg = r.cell / L.nx, x = r.cell - yg * L.nx;
-  L.base[cell_addr(L, yg - L.y0, x, r.slot)] += (int)r.count;
+// exclusive scan of n counts, three launches: per-block scans + block totals; scan of the totals (one CTA); the block
+// prefix is added by the reader (offset(i) = blocksum[i / 1024] + local[i]).  Hand-written: n <= 2^24 cells here.
+constexpr uint32_t kScanBlock = 1024;
+__device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* warp_tot /*[32] shared*/, uint32_t& total) {
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t up = __shfl_up_sync(FULL, inc, o);
+    if (lane >= (uint32_t)o) inc += up;
+  }
+  if (lane == 31) warp_tot[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = warp_tot[lane], winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(FULL, winc, o);
+      if (lane >= (uint32_t)o) winc += up;
+    }
+    warp_tot[lane] = winc - w;            // exclusive prefix of the warp totals
+    if (lane == 31) warp_tot[32] = winc;  // block total
+  }
+  __syncthreads();
+  total = warp_tot[32];
+  const uint32_t r = warp_tot[warp] + inc - v;
+  __syncthreads();
+  return r;
+}
+__global__ void __launch_bounds__(kScanBlock) scan_local_kernel(uint32_t* __restrict__ data, size_t n, uint32_t* __restrict__ blocksum) {
+  __shared__ uint32_t wt[33];
+  const size_t i = (size_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t v = i < n ? data[i] : 0u;
+  uint32_t total;
+  const uint32_t ex = block_exclusive_scan_1024(v, wt, total);
+  if (i < n) data[i] = ex;
+  if (threadIdx.x == 0) blocksum[blockIdx.x] = total;
+}
+// exclusive scan of the block totals in place (nb <= 2^24 / 1024 = 16384, a few trips of one CTA); total -> *grand
+__global__ void __launch_bounds__(kScanBlock) scan_tops_kernel(uint32_t* __restrict__ blocksum, uint32_t nb, unsigned long long* grand) {
+  __shared__ uint32_t wt[33];
+  unsigned long long carry = 0;
+  for (uint32_t base = 0; base < nb; base += kScanBlock) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < nb ? blocksum[i] : 0u;
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan_1024(v, wt, total);
+    if (i < nb) blocksum[i] = (uint32_t)carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) *grand = carry;
+}
+
+// pass 2: every event written at its final position, in (cell, slot) order; densities reduced by the mutants.
+// A CTA walks a tile in chunks of blockDim/qpr species rows.  Within a chunk the rank of an event among the events of
+// the same cell = events in lower warps (shared-memory table) + events in lower lanes of the same quad (ballot).
+__global__ void __launch_bounds__(256) mutate_emit_kernel(const Layout L, const double* __restrict__ ms, uint32_t seed,
+                                                          unsigned long long t, const uint32_t* __restrict__ offs,
+                                                          const uint32_t* __restrict__ blocksum, MutRec* __restrict__ rec) {
+  __shared__ uint32_t base[32];          // per cell of the tile: records already written
+  __shared__ uint32_t wcnt[8][32];       // per warp, per cell: events of the current chunk
+  const uint32_t ntiles = L.ntx * L.ny, qpr = L.tw / 4, per = L.nsp * qpr;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const uint32_t qd = threadIdx.x % qpr;
+  // lanes of this warp that hold the same 4 cell columns and a lower species row
+  uint32_t same_quad = 0;
+  for (uint32_t l = 0; l < 32; ++l)
+    if (l % qpr == lane % qpr) same_quad |= 1u << l;
+  const uint32_t lower = same_quad & ((1u << lane) - 1u);
+  for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int4* tp = reinterpret_cast<int4*>(L.base + (size_t)tile * L.tile_stride);
+    const uint32_t yl = tile / L.ntx, tx = tile - yl * L.ntx, yg = L.y0 + yl;
+    if (threadIdx.x < 32) {
+      const uint32_t x = tx * L.tw + threadIdx.x;
+      uint32_t b = 0;
+      if (threadIdx.x < L.tw && x < L.nx) {
+        const size_t c = (size_t)yl * L.nx + x;
+        b = blocksum[c / kScanBlock] + offs[c];
+      }
+      base[threadIdx.x] = b;
+    }
+    __syncthreads();
+    for (uint32_t i0 = 0; i0 < per; i0 += blockDim.x) {     // uniform trip count: every thread reaches the barriers
+      const uint32_t i = i0 + threadIdx.x;
+      const uint32_t s = i / qpr;
+      int born[4] = {0, 0, 0, 0};
+      int4 v = make_int4(0, 0, 0, 0);
+      if (i < per) {
+        v = tp[i];
+        mutate_born(L, v, __ldg(ms + s), tx * qpr + qd, yg, s, t, seed, born);
+      }
+      uint32_t rank[4];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t bal = __ballot_sync(FULL, born[k] > 0);
+        rank[k] = __popc(bal & lower);
+        const uint32_t tot = __popc(bal & same_quad);
+        if (lane < qpr) wcnt[warp][4 * lane + k] = tot;     // lane < qpr: one writer per (quad, k); lane % qpr == lane
+        any |= born[k] > 0;
+      }
+      __syncthreads();
+      if (any) {
+        int n[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (born[k] > 0) {
+            uint32_t pos = base[4 * qd + k] + rank[k];
+            for (uint32_t w = 0; w < warp; ++w) pos += wcnt[w][4 * qd + k];
+            rec[pos] = MutRec{yg * L.nx + tx * L.tw + 4 * qd + k, s, (uint32_t)born[k]};
+            n[k] -= born[k];
+          }
+        tp[i] = make_int4(n[0], n[1], n[2], n[3]);
+      }
+      __syncthreads();
+      if (threadIdx.x < L.tw) {
+        uint32_t add = 0;
+        for (uint32_t w = 0; w < nwarps; ++w) add += wcnt[w][threadIdx.x];
+        base[threadIdx.x] += add;
+      }
+      __syncthreads();
+    }
+  }
 }
 
 // new species rows: zero everywhere, then 1 in the birth cell (reference :272-275)

@@ -87,6 +87,7 @@ struct eco_model {
   uint64_t salt_t = 0;
   int sp_cntr = -1;   // the reference's function-static species label counter (models/ecolab_model.cc:366)
   std::vector<eco::MutRecord> pending;   // records of the last eco_mutate_cells
+  bool host_begun = false;               // eco_step_host_begin ran; eco_step_host finishes the step
 
   explicit eco_model(int dev) : eng(dev) { eng.set_grid(1, 1, 0, 1, 0); }
 
@@ -200,15 +201,27 @@ struct eco_model {
   }
 
   // generate(niter) then migrate() fed from / drained to host buffers (cell-major [cell][nsp], ascending cell id)
-  uint64_t step_host(const int32_t* in, int32_t* out, size_t ncells, size_t ns, unsigned niter) {
-    if (panmictic || y0 != 0 || nyl != numY) throw std::runtime_error("step_host: needs an unpartitioned spatial grid");
-    if (ncells != ncells_local()) throw std::runtime_error("step_host: cell count differs from the grid");
+  bool partitioned() const { return y0 != 0 || nyl != numY; }
+  void step_host_check(size_t ncells, size_t ns) {
+    if (panmictic) throw std::runtime_error("step_host: needs a spatial grid");
+    if (ncells != ncells_local()) throw std::runtime_error("step_host: cell count differs from the owned grid");
     if (tstep == 0) makeConsistent();
     grow_engine(std::max(ns, nsp()));
     check_sizes(false);
     check_sizes(true);
     if (ns != nsp()) throw std::runtime_error("step_host: species count differs from the model");
     upload();
+  }
+  void step_host_begin(const int32_t* in, size_t ncells, size_t ns, unsigned niter) {
+    step_host_check(ncells, ns);
+    if (nsp()) eng.step_host_begin(in, niter, tstep, seed);
+    host_begun = true;
+  }
+  uint64_t step_host(const int32_t* in, int32_t* out, size_t ncells, size_t ns, unsigned niter) {
+    const bool part = partitioned();
+    if (part && !host_begun) throw std::runtime_error("step_host: on a partitioned grid call eco_step_host_begin and exchange the halo first");
+    if (!part) step_host_check(ncells, ns);
+    host_begun = false;
     const size_t n = nsp();
     std::vector<double> cm(n);
     const double cap = 1.0 / maxNbrs;                                   // :628
@@ -217,7 +230,7 @@ struct eco_model {
       const double mm = (t_after - last_mig_tstep) * migration[s];      // :626 (migrate runs after tstep += niter)
       cm[s] = mm > cap ? cap : mm;                                      // :629
     }
-    const uint64_t total = n ? eng.step_host(in, out, niter, tstep, seed, cm.data()) : 0;
+    const uint64_t total = n ? eng.step_host(in, out, niter, tstep, seed, cm.data(), part) : 0;
     tstep = t_after;
     salt_t = tstep;
     last_mig_tstep = tstep;
@@ -752,7 +765,7 @@ int eco_step_host(eco_model* m, const int32_t* in, int32_t* out, size_t ncells, 
   need(m);
   if (!in || !out) throw std::runtime_error("step_host: null buffer");
   const uint64_t t = m->step_host(in, out, ncells, nsp, niter);
-  if (total) *total = t / 2;   // :702
+  if (total) *total = m->partitioned() ? t : t / 2;   // :702; a slab returns its unhalved share (summed over ranks by the caller)
   ECO_CATCH
 }
 int eco_step_async(eco_model* m, unsigned niter) {
@@ -767,6 +780,13 @@ int eco_migrate_wait(eco_model* m, uint64_t* total) {
   need(m);
   const uint64_t t = m->eng.migrate_result();
   if (total) *total = t;
+  ECO_CATCH
+}
+int eco_step_host_begin(eco_model* m, const int32_t* in, size_t ncells, size_t nsp, unsigned niter) {
+  ECO_TRY
+  need(m);
+  if (!in) throw std::runtime_error("step_host_begin: null buffer");
+  m->step_host_begin(in, ncells, nsp, niter);
   ECO_CATCH
 }
 int eco_migrate_local(eco_model* m, uint64_t* total) {

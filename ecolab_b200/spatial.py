@@ -532,16 +532,24 @@ class SpatialModel(EcolabModelBase):
         return self.migrate(wait)
 
     def step_host(self, dens_in, dens_out, niter=1):
-        """generate(niter) + migrate() on a HOST-resident state: `dens_in` [cell][nsp] int32 is uploaded, the result
-        lands in `dens_out`; copies and kernels are pipelined over bands of grid rows (eco_step_host)."""
-        if self.world != 1:
-            raise EcolabError("step_host: unpartitioned grids only")
+        """generate(niter) + migrate() on a HOST-resident state: `dens_in` [owned cell][nsp] int32 is uploaded, the result
+        lands in `dens_out`; copies and kernels are pipelined over bands of grid rows (eco_step_host).  Under
+        torch.distributed each rank streams its own slab over its own PCIe link; the slab's two boundary rows are
+        generated first so that the halo exchange does not wait for the upload."""
         a, b = np.ascontiguousarray(dens_in, dtype=np.int32), dens_out
         if b.dtype != np.int32 or not b.flags.c_contiguous or b.shape != a.shape:
             raise EcolabError("step_host: dens_out must be a C-contiguous int32 array shaped like dens_in")
         t = C.c_uint64()
+        if self.world == 1:
+            check(self._L.eco_step_host(self._h, _ptr(a), _ptr(b), a.shape[0], a.shape[1], int(niter), C.byref(t)))
+            return t.value
+        check(self._L.eco_step_host_begin(self._h, _ptr(a), a.shape[0], a.shape[1], int(niter)))
+        ht = self.halo_tensors()
+        if ht is not None:
+            self._comm.sendrecv_rows(*ht)
+            self.halo_done()
         check(self._L.eco_step_host(self._h, _ptr(a), _ptr(b), a.shape[0], a.shape[1], int(niter), C.byref(t)))
-        return t.value
+        return self._comm.allreduce_sum(t.value) // 2
 
     def condense(self):
         if self.world == 1:

@@ -120,7 +120,12 @@ int eco_migrate_wait(eco_model* m, uint64_t* abs_delta_sum);
  * [cell][nsp], ascending cell id, as eco_set/get_density_all; pinned memory makes the copies asynchronous).  Equivalent
  * to eco_set_density_all(in); eco_step(niter); eco_get_density_all(out) -- i.e. SpatialModel::generate :607-614 +
  * ::migrate :616-703 on densities set through EcolabPoint::density (models/ecolab_model.h:88) -- but streamed in
- * bands of grid rows so that H2D, the kernels and D2H overlap.  Unpartitioned grids only. */
+ * bands of grid rows so that H2D, the kernels and D2H overlap.
+ * On a slab of a partitioned grid (eco_set_grid_slab) the step has two halves around the halo exchange: eco_step_host_begin
+ * uploads and generates the slab's first and last grid row, the host language then exchanges the halo rows (eco_halo_ptrs +
+ * send/recv, or nothing once eco_peer_connect is live), and eco_step_host streams the rest; *total is then this slab's
+ * UNHALVED sum|delta| (as eco_migrate_local). */
+int eco_step_host_begin(eco_model* m, const int32_t* in, size_t ncells, size_t nsp, unsigned niter);
 int eco_step_host(eco_model* m, const int32_t* in, int32_t* out, size_t ncells, size_t nsp, unsigned niter, uint64_t* total);
 /* SpatialModel::condense :171-196 / PanmicticModel::condense :161-169; *removed = #extinct species */
 int eco_condense(eco_model* m, unsigned* removed);

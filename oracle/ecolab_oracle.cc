@@ -550,6 +550,29 @@ struct Oracle {
     return sum / (species.size() * (species.size() - 1));
   }
 
+  // models/ecolab_model.cc:493-503 PanmicticModel::mutantConnectivity: the masked sum runs in entry order (`sum(x, mask)`,
+  // include/arrays.h:2303-2330); note the strict `>` on row/col, as in the reference
+  Float mutantConnectivity(size_t beforeNsp) const {
+    const size_t n = species.size() - beforeNsp;
+    if (species.size() <= beforeNsp) return 0;
+    Float sum = 0;
+    for (size_t j = 0; j < val.size(); ++j)
+      if (row[j] > beforeNsp || col[j] > beforeNsp) sum += (val[j] * val[j]) / (diag[row[j]] * diag[col[j]]);
+    return sum / (n * (species.size() - 1));
+  }
+
+  // models/ecolab_model.cc:506-516 PanmicticModel::extinctionConnectivity
+  Float extinctionConnectivity() const {
+    const auto& d = cells[0].n;
+    size_t n = 0;
+    for (int v : d) n += v == 0;
+    if (n == 0) return 0;
+    Float sum = 0;
+    for (size_t j = 0; j < val.size(); ++j)
+      if (d[row[j]] == 0 || d[col[j]] == 0) sum += (val[j] * val[j]) / (diag[row[j]] * diag[col[j]]);
+    return sum / (n * (species.size() - 1));
+  }
+
   // models/ecolab_model.cc:474-490 PanmicticModel::lifetimes
   std::vector<Float> lifetimes() {
     std::vector<Float> out;
@@ -716,6 +739,8 @@ void orc_mutate_model(void* h, const uint32_t* parents, size_t m) {
 }
 void orc_random_interaction(void* h, unsigned conn, double sigma) { ((Oracle*)h)->random_interaction(conn, sigma); }
 double orc_connectivity(void* h) { return ((Oracle*)h)->connectivity(); }
+double orc_mutant_connectivity(void* h, size_t before) { return ((Oracle*)h)->mutantConnectivity(before); }
+double orc_extinction_connectivity(void* h) { return ((Oracle*)h)->extinctionConnectivity(); }
 long orc_lifetimes(void* h, double* out, size_t cap) {
   auto v = ((Oracle*)h)->lifetimes();
   std::copy(v.begin(), v.begin() + std::min(cap, v.size()), out);

@@ -74,6 +74,8 @@ def lib():
             "orc_mutate_model": (None, [vp, vp, sz]),
             "orc_random_interaction": (None, [vp, C.c_uint, dbl]),
             "orc_connectivity": (dbl, [vp]),
+            "orc_mutant_connectivity": (dbl, [vp, sz]),
+            "orc_extinction_connectivity": (dbl, [vp]),
             "orc_lifetimes": (C.c_long, [vp, vp, sz]),
             "orc_nsp_per_cell": (None, [vp, vp]),
             "orc_get_pre": (C.c_long, [vp, vp, sz]),
@@ -242,6 +244,12 @@ class Oracle:
 
     def connectivity(self):
         return self.L.orc_connectivity(self.h)
+
+    def mutant_connectivity(self, before_nsp):
+        return self.L.orc_mutant_connectivity(self.h, int(before_nsp))
+
+    def extinction_connectivity(self):
+        return self.L.orc_extinction_connectivity(self.h)
 
     def lifetimes(self):
         a = np.empty(max(self.nsp, 1), dtype=np.float64)

@@ -87,3 +87,53 @@ def oracle_density(o, grid):
     if grid:
         return o.get_density_all()
     return np.array([o.get_density(0)], dtype=np.int32)
+
+
+# ---------------------------------------------------------------------------------------------
+# band parity at sizes the oracle cannot hold whole (BASELINE.json C3 / C4): generate is independent per cell and
+# migrate reaches one row up and down, so rows [y, y+nb) after generate(1)+migrate() depend only on rows [y-1, y+nb+1)
+# before it.  The oracle runs that 6-row slab with the true global row numbers (the Philox stream is keyed on them).
+# ---------------------------------------------------------------------------------------------
+def collect_rows(m, y, n):
+    """Grid rows [y, y+n) as [n*nx][nsp] int32 on rank 0 (None elsewhere); the rows may straddle rank seams."""
+    world = getattr(m, "world", 1)
+    if world == 1:
+        return m.density_rows(y, n)
+    import torch.distributed as dist
+    a, b = max(y, m._y0), min(y + n, m._y1)
+    part = (a, m.density_rows(a, b - a)) if b > a else None
+    parts = [None] * world if m.rank == 0 else None
+    dist.gather_object(part, parts, dst=0)
+    if m.rank != 0:
+        return None
+    parts = sorted((q for q in parts if q is not None), key=lambda q: q[0])
+    return np.concatenate([q[1] for q in parts])
+
+
+def band_step_equals_oracle(O, m, p, scalars, seed, y, nb=4):
+    """Run ONE generate(1)+migrate() step on the GPU model `m` (any size, any partition) and check rows [y, y+nb) of the
+    result against the oracle fed with the GPU's own pre-step rows [y-1, y+nb+1).  Collective under torch.distributed;
+    returns (equal, moved) on rank 0 and (None, moved) elsewhere."""
+    nx, ny = m._nx, m._ny
+    ya, yb = max(0, y - 1), min(ny, y + nb + 1)
+    pre = collect_rows(m, ya, yb - ya)
+    tstep, last_mig = m.tstep(), m.last_mig_tstep()
+    moved = m.step(1)
+    post = collect_rows(m, y, nb)
+    if pre is None:
+        return None, moved
+    ns = pre.shape[1]
+    o = O.Oracle(rng=O.RNG_PHILOX, seed=seed)
+    for k, v in scalars.items():
+        o.set(k, v)
+    for k, v in p.items():
+        o.set(k, v)
+    o.set_grid_slab(nx, ny, ya, yb - ya)
+    o.set_density_all(pre)
+    zeros = np.zeros((nx, ns), dtype=np.int32)
+    o.set_ghost(0, zeros); o.set_ghost(1, zeros)      # only reach the slab's outer rows, which are not compared
+    o.set("tstep", tstep); o.set("last_mig_tstep", last_mig)
+    o.generate(1)
+    o.migrate_local()
+    want = o.get_density_all()[(y - ya) * nx:(y - ya + nb) * nx]
+    return bool(np.array_equal(post, want)), moved

@@ -20,11 +20,14 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     comm = E.Comm()
-    nx, ny, nsp, k, seed = 37, 11, 45, 3, 7
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)                 # kernels and NCCL on one stream: the configuration bench.py runs
+    nx, ny, nsp, k, seed = 37, 19, 45, 3, 7
     p = synth(nsp, k, seed, mig=0.07, mut=2e-3)
     d = densities(nx * ny, nsp, seed)
     d[:, 4] = 0                                   # one species extinct everywhere -> condense removes it on every rank
     m = E.SpatialModel(local, comm)
+    m.set_stream(stream)
     for kk, v in SCALARS.items():
         getattr(m, kk)(v)
     m.mut_max(2e-3)
@@ -46,8 +49,8 @@ def main():
         return torch.cat(outs).cpu().numpy()
 
     o = None
+    from oracle import oracle as O
     if rank == 0:
-        from oracle import oracle as O
         O.build()
         sc = dict(SCALARS); sc["mut_max"] = 2e-3
         o = load_oracle(O, p, d, (nx, ny), seed=seed, scalars=sc)
@@ -70,10 +73,14 @@ def main():
     if rank == 0:
         assert removed == o.condense() and removed >= 1
     check("condense")
-    # mutate: the cell-side speciation is deterministic (Philox); the parameter draws use rank 0's libc stream,
-    # so compare what must agree: species counts on every rank, conservation of individuals, parents' loss
+    # mutate: the cell-side speciation is deterministic (Philox); the parameter draws come from rank 0's libc stream
+    # (ModelData::mutate runs on rank 0 only, :251-258), seeded here exactly like the oracle's -> everything must be equal
     before = int(gathered().sum())
     nsp0 = len(m.species)
+    if rank == 0:
+        O.srand(123); O.reset_grand()
+        o.mutate()
+        O.srand(123); E.lib().eco_array_grand_reset()
     m.mutate()
     nsp1 = len(m.species)
     t = torch.tensor([nsp1], device="cuda")
@@ -82,16 +89,72 @@ def main():
     assert int(lo) == int(hi) == nsp1 and nsp1 > nsp0, "every rank must append the same mutants"
     g = gathered()
     assert g.shape[1] == nsp1 and int(g.sum()) == before, "mutation moves individuals, it does not create them"
-    assert (g[:, nsp0:].sum(axis=0) == 1).all(), "each mutant is born as one individual in one cell"
-    rr = torch.tensor(np.asarray(m.repro_rate()), device="cuda")
-    r0 = rr.clone(); dist.broadcast(r0, 0)
-    assert torch.equal(rr, r0), "species parameters must be replicated identically"
-    m.generate(2); moved = m.migrate()
-    g = gathered()
-    assert (g >= 0).all()
+    if rank == 0:
+        assert nsp1 == o.nsp
+        assert np.array_equal(g, o.get_density_all()), "mutate densities"
+    for name in ("repro_rate", "mutation", "migration", "create"):
+        mine = torch.tensor(np.asarray(getattr(m, name)()), device="cuda")
+        r0 = mine.clone(); dist.broadcast(r0, 0)
+        assert torch.equal(mine, r0), f"{name} must be replicated identically"
+        if rank == 0:
+            assert np.array_equal(mine.cpu().numpy(), o.get(name)), f"{name} vs oracle"
+    for name in ("diag", "val", "row", "col"):
+        mine = torch.tensor(np.asarray(getattr(m.interaction, name)(), dtype=np.float64), device="cuda")
+        r0 = mine.clone(); dist.broadcast(r0, 0)
+        assert torch.equal(mine, r0), f"interaction.{name} must be replicated identically"
+        if rank == 0:
+            assert np.array_equal(mine.cpu().numpy(), o.get("interaction." + name).astype(np.float64)), f"interaction.{name} vs oracle"
+    if rank == 0:
+        assert m.species() == o.get("species").tolist()
+    # the mutated model drives the next steps identically (capacity growth re-allocates the buffers: the peer-memory halo
+    # has to reconnect), then condense again
+    for it in range(2):
+        m.generate(2)
+        if rank == 0:
+            o.generate(2)
+        moved = m.migrate()
+        if rank == 0:
+            assert moved == o.migrate(), "migrate total after mutate"
+        check(f"after mutate {it}")
+    removed = m.condense()
+    if rank == 0:
+        assert removed == o.condense()
+    check("second condense")
+    # non-blocking steps (no host round trip per step), total fetched at the end
+    for _ in range(3):
+        m.step(1, wait=False)
+        if rank == 0:
+            o.generate(1); want_moved = o.migrate()
+    moved = m.last_migration()
+    if rank == 0:
+        assert moved == want_moved
+    check("async steps")
+    # host-resident state streamed through every rank's own PCIe link (eco_step_host_begin / halo / eco_step_host)
+    loc_in = m.density_array()
+    loc_out = np.empty_like(loc_in)
+    moved = m.step_host(loc_in, loc_out, 2)
+    if rank == 0:
+        o.generate(2)
+        assert moved == o.migrate(), "step_host total"
+    check("step_host device state")
+    assert np.array_equal(loc_out, m.density_array()), "step_host host result"
+    # the scripts' view of a distributed model: whole-grid nsp(), collective cell reads, dropped remote writes
+    ns_all = m.nsp()
+    if rank == 0:
+        assert ns_all == o.nsp_per_cell().tolist()
+    probe = m.cell(nx - 1, ny - 1).density()          # owned by the last rank, read everywhere
+    if rank == 0:
+        assert probe == o.get_density((nx - 1) + nx * (ny - 1)).tolist()
+    m.cell(0, 0).density(probe)                       # every rank executes it; only the owner (rank 0) stores it
+    if rank == 0:
+        o.set_density(0, np.array(probe, dtype=np.int32))
+    check("spmd cell write")
+    halo = "peer" if int(m._scalar("peer_connected")) else "nccl"
+    want_halo = os.environ.get("ECOLAB_B200_HALO", "peer")
+    assert halo == want_halo or m._peer_failed, (halo, want_halo)
     dist.barrier()
     if rank == 0:
-        print("MULTI_GPU_OK", world)
+        print("MULTI_GPU_OK", world, halo)
     dist.destroy_process_group()
 
 

@@ -18,12 +18,17 @@ def _port():
     return p
 
 
-@pytest.mark.parametrize("world", [2, 4])
-def test_partitioned_model_matches_oracle(world):
+@pytest.mark.parametrize("halo", ["peer", "nccl"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_partitioned_model_matches_oracle(world, halo):
+    """Row-slab partition over `world` GPUs against the single-process oracle of the whole grid: generate, migrate (halo
+    rows read out of the neighbours' memory over NVLink, or exchanged through NCCL), condense, mutate incl. the new species'
+    parameters, buffer re-allocation, non-blocking steps, the scripts' SPMD cell access."""
     import torch
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", str(_port()), os.path.join(HERE, "multi_gpu_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and f"MULTI_GPU_OK {world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+    env = dict(os.environ, ECOLAB_B200_HALO=halo)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and f"MULTI_GPU_OK {world} {halo}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -4,7 +4,9 @@ generate is independent per cell, so any block of cells can be verified against 
 import numpy as np
 import pytest
 
-from helpers import SCALARS, load_oracle, synth
+import gc
+
+from helpers import SCALARS, band_step_equals_oracle, densities, load_gpu, load_oracle, synth
 
 pytestmark = pytest.mark.gpu
 
@@ -67,3 +69,59 @@ def test_c3_conservation_determinism_and_block_parity(oracle_mod, gpu):
     a = np.array(m.cell(1023, 1023).density()); b = np.array(m2.cell(1023, 1023).density())
     assert np.array_equal(a, b)
     assert min(m.nsp()) > 0
+
+
+def test_c2_exact_shape_full_cadence(oracle_mod, gpu):
+    """BASELINE.json config 2 at its exact shape: 64 x 64 cells, 1000 species, 50 off-diagonal terms per row (~5 %
+    connectivity), generate(3) + migrate + mutate + condense, every density and every model array against the oracle."""
+    O = oracle_mod
+    grid, nsp, k = (64, 64), 1000, 50
+    p = synth(nsp, k, 2, mut=2e-5)
+    scal = dict(SCALARS, mut_max=2e-5)
+    d = densities(grid[0] * grid[1], nsp, 2)
+    d[:, [17, 500, 999]] = 0                         # extinct everywhere: condense has something to remove
+    o = load_oracle(O, p, d, grid, seed=10, scalars=scal)
+    m = load_gpu(gpu, p, d, grid, seed=10, scalars=scal)
+    for rnd in range(2):
+        o.generate(3); m.generate(3)
+        assert np.array_equal(m.density_array(), o.get_density_all()), f"generate, round {rnd}"
+        assert m.migrate() == o.migrate()
+        assert np.array_equal(m.density_array(), o.get_density_all()), f"migrate, round {rnd}"
+        O.srand(40 + rnd); O.reset_grand(); o.mutate()
+        O.srand(40 + rnd); gpu.lib().eco_array_grand_reset(); m.mutate()
+        assert len(m.species) == o.nsp
+        assert m.condense() == o.condense()
+        assert np.array_equal(m.density_array(), o.get_density_all()), f"mutate+condense, round {rnd}"
+        for name in ("diag", "val", "row", "col"):
+            assert np.array_equal(np.array(getattr(m.interaction, name)()), o.get("interaction." + name)), name
+    assert len(m.species) != nsp                      # species were removed and added
+
+
+def _band_model(gpu, nx, ny, nsp, k):
+    m, p = build(gpu, nx, ny, nsp, k)
+    m.fill_density_random(0, 199)
+    return m, p
+
+
+@pytest.mark.parametrize("n", [1024, 4096])
+def test_band_parity_at_c3_and_c4(oracle_mod, gpu, n):
+    """C3 (1024^2 x 1024) and C4 (4096^2 x 1024, 128 GiB of device buffers): after generate(1)+migrate() on the FULL grid,
+    4-row bands at the top, in the middle (where an 8-GPU partition has a seam) and at the bottom equal the oracle run on
+    the GPU's own pre-step rows; per-species totals are conserved by migrate at full size."""
+    import torch
+    gc.collect()
+    free, _ = torch.cuda.mem_get_info()
+    need = 2 * (n * (n + 2)) * 1024 * 4 + (3 << 30)
+    if free < need:
+        pytest.skip(f"needs {need >> 30} GiB of free device memory, {free >> 30} GiB available")
+    m, p = _band_model(gpu, n, n, 1024, 3)
+    for y in (0, n // 2 - 2, n - 4):
+        ok, moved = band_step_equals_oracle(oracle_mod, m, p, SCALARS, 10, y)
+        assert ok, f"band at row {y}"
+        assert moved > 0
+    m.generate(1)
+    tot = m.species_totals()
+    m.migrate()
+    assert np.array_equal(m.species_totals(), tot)
+    del m
+    gc.collect()
