@@ -12,6 +12,11 @@ driver scripts (models/*.py) run unchanged:
 import os
 import sys
 
+import importlib.util
+
 _here = os.path.dirname(os.path.abspath(__file__))
 if _here not in sys.path:
     sys.path.insert(0, _here)
+# models/panmictic_ecolab.py imports tkinter unconditionally; interpreters built without it get an inert stand-in
+if importlib.util.find_spec("tkinter") is None:
+    sys.path.append(os.path.join(_here, "_stubs"))

@@ -180,6 +180,24 @@ __device__ __forceinline__ void mig_edge_offsets(const Layout& L, uint32_t x0, u
   eo_e = has_r ? (long long)L.tile_stride - (long long)(tw - 4) : 3;
 }
 
+// publish this rank's epoch counter to the neighbour ranks (they map it through CUDA IPC)
+__global__ void flag_publish_kernel(unsigned int* flag, unsigned int value) {
+  __threadfence_system();   // everything this stream did before is visible to the peers before the counter moves
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
+// poll a neighbour rank's "generate done" counter (peer memory over NVLink); bounded so that a lost peer cannot hang the GPU
+__device__ __forceinline__ void mig_wait_flag(const unsigned int* flag, unsigned int epoch, unsigned int* err) {
+  const long long t0 = clock64();
+  for (;;) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if ((int)(v - epoch) >= 0) return;
+    if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); return; }   // ~10 s
+    __nanosleep(200);
+  }
+}
+
 template <int TW>
 __global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams p) {
   constexpr int QPR = TW / 4, RW = 32 / QPR;   // lanes per species row, species rows per warp
@@ -210,6 +228,14 @@ __global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams
     const int32_t* ps = L.y0 + ye >= L.nyg ? p0 + (long long)(n - 1) * stride
                                            : (ye == L.ny ? p.bottom_row + lane_off : p0 + (long long)n * stride);
     int32_t* dp = p.dst + (size_t)ys * L.row_stride + lane_off;
+    // peer-memory halo: a unit that touches a neighbour rank's row first waits for that rank's epoch counter
+    if ((p.top_flag && ys == 0 && L.y0 != 0) || (p.bottom_flag && ye == L.ny && L.y0 + ye < L.nyg)) {
+      if (lane == 0) {
+        if (p.top_flag && ys == 0 && L.y0 != 0) mig_wait_flag(p.top_flag, p.epoch, p.err);
+        if (p.bottom_flag && ye == L.ny && L.y0 + ye < L.nyg) mig_wait_flag(p.bottom_flag, p.epoch, p.err);
+      }
+      __syncwarp();
+    }
     const bool ragged = (tx + 1) * TW > L.nx;      // warp-uniform: the ragged last tile
     const uint32_t rag = 1u + (x0 >= L.nx ? 0u : min(5u, L.nx - x0));
     if (ragged) mig_unit<DUALE, true, kMigRowsInFlight>(p0, pn, ps, dp, stride, n, eoff, eo_e, c, first_q, last_q, rag, acc);
@@ -236,24 +262,6 @@ __global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams
 // =====================================================================================================================
 constexpr int kMigPipeWarps = 16;     // consumer warps
 constexpr int kMigPipeEdge = 4;       // rows the extra-cell loads run ahead
-
-// publish this rank's epoch counter to the neighbour ranks (they map it through CUDA IPC)
-__global__ void flag_publish_kernel(unsigned int* flag, unsigned int value) {
-  __threadfence_system();   // everything this stream did before is visible to the peers before the counter moves
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
-}
-
-// poll a neighbour rank's "generate done" counter (peer memory over NVLink); bounded so that a lost peer cannot hang the GPU
-__device__ __forceinline__ void mig_wait_flag(const unsigned int* flag, unsigned int epoch, unsigned int* err) {
-  const long long t0 = clock64();
-  for (;;) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-    if ((int)(v - epoch) >= 0) return;
-    if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); return; }   // ~10 s
-    __nanosleep(200);
-  }
-}
 
 template <int TW, int NS, bool RAG>
 __device__ __forceinline__ void migp_unit(const MigParams& p, uint32_t tx, uint32_t g, uint32_t ys, uint32_t n, uint32_t warp,
@@ -302,8 +310,11 @@ __device__ __forceinline__ void migp_unit(const MigParams& p, uint32_t tx, uint3
         "DONE_%=:\n\t}" ::"r"(full_s + 8u * stage), "r"(phase) : "memory");
     const uint32_t a = ring_s + stage * stage_bytes;
 #pragma unroll
-    for (int s = 0; s < NS; ++s)
-      asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v[s].x), "=r"(v[s].y), "=r"(v[s].z), "=r"(v[s].w) : "r"(a + soff[s]) : "memory");
+    for (int s = 0; s < NS; ++s) {
+      v[s] = make_int4(0, 0, 0, 0);
+      if (valid[s])   // warp-uniform; a block past the species capacity has no bytes in the slot
+        asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v[s].x), "=r"(v[s].y), "=r"(v[s].z), "=r"(v[s].w) : "r"(a + soff[s]) : "memory");
+    }
     __syncwarp();
     if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_s + 8u * stage) : "memory");
     if (++stage == p.nstages) { stage = 0; phase ^= 1u; }

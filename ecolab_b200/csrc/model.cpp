@@ -26,7 +26,39 @@ thread_local std::string g_err;
 // array_urand: libc rand()/RAND_MAX (src/random.cc:57); array_grand: running-CLT
 // generator (src/random.cc:59-64).  Kept semantically identical so that
 // `array_urand.seed(n)` in the driver scripts means the same thing.
-inline double urand01() { return ((double)::rand()) / RAND_MAX; }
+//
+// rand() here is glibc's: the additive feedback generator r[i] = r[i-3] + r[i-31] (TYPE_3 of random_r, seeded by the
+// Lehmer sequence 16807*x mod 2^31-1, first 310 outputs discarded, low bit dropped), restated so that the model OWNS the
+// state.  Two reasons: ModelData::mutate draws a gaussian for every element of two dense temporaries per mutant
+// (do_row_or_col, :351-358) -- millions of calls per mutate at 1000 species -- and libc's rand() takes a lock per call
+// (29 ns vs 2 ns here); and an owned state goes into the checkpoint, so a restarted run draws the same parameters.
+// The tests run it side by side with libc rand() (the oracle's) from the same seeds: identical streams.
+constexpr int kRandMax = 2147483647;
+struct GlibcRand {
+  int32_t r[31];
+  int32_t f = 3, b = 0;
+  GlibcRand() { seed(1); }   // an unseeded libc generator behaves like srand(1)
+  void seed(unsigned s) {
+    if (s == 0) s = 1;
+    r[0] = (int32_t)s;
+    int32_t word = (int32_t)s;
+    for (int i = 1; i < 31; ++i) {
+      const long hi = word / 127773, lo = word % 127773;
+      word = (int32_t)(16807 * lo - 2836 * hi);
+      if (word < 0) word += 2147483647;
+      r[i] = word;
+    }
+    f = 3; b = 0;
+    for (int k = 0; k < 310; ++k) next();
+  }
+  int next() {
+    const uint32_t val = (uint32_t)r[f] + (uint32_t)r[b];
+    r[f] = (int32_t)val;
+    if (++f >= 31) { f = 0; ++b; } else if (++b >= 31) b = 0;
+    return (int)(val >> 1);
+  }
+} g_urand;
+inline double urand01() { return ((double)g_urand.next()) / kRandMax; }
 struct RunningClt {
   double sum = 0;
   unsigned n = 0;
@@ -277,7 +309,7 @@ struct eco_model {
 
   // do_row_or_col, models/ecolab_model.cc:327-359
   void perturb_links(std::vector<double>& t, double range, double minval, double gd) {
-    double r = (2.0 * ::rand()) / RAND_MAX - 1 + gen_bias;
+    double r = (2.0 * g_urand.next()) / kRandMax - 1 + gen_bias;
     r = r > 0 ? r / (1 + gen_bias) : r / (1 - gen_bias);
     size_t cnt = t.size();
     if (r != 0) {
@@ -287,9 +319,9 @@ struct eco_model {
     cnt = std::min(cnt, t.size());
     const double span = (double)(t.size() - 1);
     for (size_t j = 0; j < cnt; ++j) {
-      const int pos = (int)(span * ((double)::rand() / RAND_MAX) + .5);
+      const int pos = (int)(span * ((double)g_urand.next() / kRandMax) + .5);
       if (r > 0) {
-        if (t[pos] == 0.0) t[pos] = range * ((double)::rand() / RAND_MAX) + minval;
+        if (t[pos] == 0.0) t[pos] = range * ((double)g_urand.next() / kRandMax) + minval;
       } else
         t[pos] = 0;
     }
@@ -334,14 +366,19 @@ struct eco_model {
     }
 
     const double range = odiag_max - odiag_min;
+    // entries of every row / column in COO order (the reference scans the whole COO per mutant, :414-423; the lists give
+    // the same scatter order -- a later duplicate overwrites an earlier one -- in O(row length)); entries appended by an
+    // earlier mutant of this batch are seen by a later one, as in the reference
+    std::vector<std::vector<uint32_t>> byrow(n0 + m), bycol(n0 + m);
+    for (size_t j = 0; j < row.size(); ++j) { byrow[row[j]].push_back((uint32_t)j); bycol[col[j]].push_back((uint32_t)j); }
     for (size_t i = 0; i < m; ++i) {
       const size_t L = n0 + i;   // index of the new species; length of the dense temporaries (:411)
       const uint32_t p = parents[i];
       std::vector<double> rw(L, 0.0), cl(L, 0.0);
-      for (size_t j = 0; j < row.size(); ++j) if (row[j] == p) rw[col[j]] = val[j];
+      for (uint32_t j : byrow[p]) if (col[j] < L) rw[col[j]] = val[j];
       rw[p] = diag[p];
       perturb_links(rw, range, odiag_min, gd[i]);
-      for (size_t j = 0; j < col.size(); ++j) if (col[j] == p) cl[row[j]] = val[j];
+      for (uint32_t j : bycol[p]) if (row[j] < L) cl[row[j]] = val[j];
       cl[p] = diag[p];
       perturb_links(cl, range, odiag_min, gd[i]);
 
@@ -359,8 +396,16 @@ struct eco_model {
           if (b) cl[q] = cl[q] - s / nadj;
         }
       }
-      for (size_t q = 0; q < L; ++q) if (rw[q] != 0.0) { val.push_back(rw[q]); row.push_back((uint32_t)L); col.push_back((uint32_t)q); }
-      for (size_t q = 0; q < L; ++q) if (cl[q] != 0.0) { val.push_back(cl[q]); row.push_back((uint32_t)q); col.push_back((uint32_t)L); }
+      for (size_t q = 0; q < L; ++q)
+        if (rw[q] != 0.0) {
+          byrow[L].push_back((uint32_t)val.size()); bycol[q].push_back((uint32_t)val.size());
+          val.push_back(rw[q]); row.push_back((uint32_t)L); col.push_back((uint32_t)q);
+        }
+      for (size_t q = 0; q < L; ++q)
+        if (cl[q] != 0.0) {
+          byrow[q].push_back((uint32_t)val.size()); bycol[L].push_back((uint32_t)val.size());
+          val.push_back(cl[q]); row.push_back((uint32_t)q); col.push_back((uint32_t)L);
+        }
     }
     for (size_t k = 0; k < m; ++k) { create.push_back(0); species.push_back((int32_t)(k * nprocs) + sp_cntr); }
     sp_cntr += (int)(m * nprocs);
@@ -412,7 +457,7 @@ struct eco_model {
       } else {
         std::vector<bool> seen(n);
         for (size_t q = 0; q < pick.size();) {
-          const size_t j = (size_t)((n * (double)::rand()) / RAND_MAX);
+          const size_t j = (size_t)((n * (double)g_urand.next()) / kRandMax);
           if (j < n && !seen[j]) { seen[j] = true; pick[q++] = (int)j; }
         }
       }
@@ -894,7 +939,7 @@ int eco_species_totals(eco_model* m, int64_t* out, size_t nsp) {
 
 // ---- checkpoint / restart: self-describing little-endian dump -------------------------
 namespace {
-const char kMagic[8] = {'E', 'C', 'O', 'B', '2', '0', '0', 2};
+const char kMagic[8] = {'E', 'C', 'O', 'B', '2', '0', '0', 3};
 template <class T> void wr(FILE* f, const T& v) { if (fwrite(&v, sizeof v, 1, f) != 1) throw std::runtime_error("checkpoint: write failed"); }
 template <class T> void rd(FILE* f, T& v) { if (fread(&v, sizeof v, 1, f) != 1) throw std::runtime_error("restart: truncated file"); }
 template <class T> void wrv(FILE* f, const std::vector<T>& v) {
@@ -923,9 +968,11 @@ int eco_checkpoint(eco_model* m, const char* file) {
   wr(f, m->sp_sep); wr(f, m->mut_max); wr(f, m->repro_min); wr(f, m->repro_max); wr(f, m->odiag_min); wr(f, m->odiag_max); wr(f, m->gen_bias);
   wr(f, (uint8_t)m->fixMutation); wr(f, (uint8_t)m->fixMigration);
   wr(f, m->seed); wr(f, m->salt_t); wr(f, (int32_t)m->sp_cntr);
-  // the process-wide running-CLT gaussian generator (array_grand, src/random.cc:59-64) and the rank count that spaces the
-  // species labels (:462); libc rand() keeps its own state and is, as in the reference, not part of a checkpoint
+  // the process-wide generators (array_urand, array_grand, src/arrays.cc:24-25) and the rank count that spaces the species
+  // labels (:462): with them a restarted run also draws the same new-species parameters (the reference saves neither)
   wr(f, (uint32_t)m->nprocs); wr(f, g_grand.sum); wr(f, (uint32_t)g_grand.n);
+  for (int32_t v : g_urand.r) wr(f, v);
+  wr(f, g_urand.f); wr(f, g_urand.b);
   wrv(f, m->species); wrv(f, m->create); wrv(f, m->repro_rate); wrv(f, m->mutation); wrv(f, m->migration);
   wrv(f, m->diag); wrv(f, m->val); wrv(f, m->row); wrv(f, m->col);
   const size_t ns = m->eng.nsp();
@@ -955,6 +1002,9 @@ int eco_restart(eco_model* m, const char* file) {
   uint32_t np, gn;
   rd(f, np); rd(f, g_grand.sum); rd(f, gn);
   m->nprocs = np; g_grand.n = gn;
+  for (int32_t& v : g_urand.r) rd(f, v);
+  rd(f, g_urand.f); rd(f, g_urand.b);
+  if (g_urand.f < 0 || g_urand.f > 30 || g_urand.b < 0 || g_urand.b > 30) throw std::runtime_error("restart: corrupt generator state");
   rdv(f, m->species); rdv(f, m->create); rdv(f, m->repro_rate); rdv(f, m->mutation); rdv(f, m->migration);
   rdv(f, m->diag); rdv(f, m->val); rdv(f, m->row); rdv(f, m->col);
   uint64_t ns; rd(f, ns);
@@ -1050,7 +1100,7 @@ int eco_append_species(eco_model* m, const uint32_t* cells, size_t n) {
   ECO_CATCH
 }
 
-void eco_array_urand_seed(int seed) { srand((unsigned)seed); }
+void eco_array_urand_seed(int seed) { g_urand.seed((unsigned)seed); }
 void eco_array_grand_reset(void) { g_grand = RunningClt(); }
 
 int eco_set_tuning(eco_model* m, const char* knob, int value) {
@@ -1060,6 +1110,7 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
   else if (k == "mig_variant") m->eng.mig_variant = value;
   else if (k == "mig_stages") m->eng.mig_stages = value;
+  else if (k == "mig_rows") m->eng.mig_rows = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
   else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;
   else if (k == "gen_dual") m->eng.gen_dual = value;

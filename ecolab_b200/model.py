@@ -42,7 +42,10 @@ class EcoList(list):
     back wrapped arrays for method results (``ecolab.nsp()()``,
     models/spatial_ecolab.py:46)."""
 
-    _properties = ()
+    @property
+    def _properties(self):
+        """The plain value behind the wrapper (`ecolab.density()._properties`, models/pred-prey.py:23)."""
+        return list(self)
 
     def __call__(self):
         return list(self)

@@ -280,6 +280,7 @@ struct Oracle {
   void generate(unsigned niter) {
     if (tstep == 0) makeConsistent();
     const size_t ns = nsp();
+    if (rowlist.size() != ns) computeODiagIdx();   // a model loaded mid-run (tstep set by hand) never went through makeConsistent
     if (record_pre) pre.assign(cells.size() * ns, 0);
     const long ncell = (long)cells.size();
 #pragma omp parallel for schedule(static)

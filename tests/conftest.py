@@ -28,3 +28,6 @@ def gpu():
     import ecolab_b200
     ecolab_b200.lib()
     return ecolab_b200
+
+# verbatim driver scripts of the reference (fixtures run by test_gpu_ref_scripts.py), not test modules
+collect_ignore = ["ref_scripts"]

@@ -132,6 +132,7 @@ def band_step_equals_oracle(O, m, p, scalars, seed, y, nb=4):
     o.set_density_all(pre)
     zeros = np.zeros((nx, ns), dtype=np.int32)
     o.set_ghost(0, zeros); o.set_ghost(1, zeros)      # only reach the slab's outer rows, which are not compared
+    o.make_consistent()
     o.set("tstep", tstep); o.set("last_mig_tstep", last_mig)
     o.generate(1)
     o.migrate_local()

@@ -80,7 +80,7 @@ def main():
     if rank == 0:
         O.srand(123); O.reset_grand()
         o.mutate()
-        O.srand(123); E.lib().eco_array_grand_reset()
+        E.lib().eco_array_urand_seed(123); E.lib().eco_array_grand_reset()
     m.mutate()
     nsp1 = len(m.species)
     t = torch.tensor([nsp1], device="cuda")

@@ -88,7 +88,7 @@ def test_c2_exact_shape_full_cadence(oracle_mod, gpu):
         assert m.migrate() == o.migrate()
         assert np.array_equal(m.density_array(), o.get_density_all()), f"migrate, round {rnd}"
         O.srand(40 + rnd); O.reset_grand(); o.mutate()
-        O.srand(40 + rnd); gpu.lib().eco_array_grand_reset(); m.mutate()
+        gpu.lib().eco_array_urand_seed(40 + rnd); gpu.lib().eco_array_grand_reset(); m.mutate()
         assert len(m.species) == o.nsp
         assert m.condense() == o.condense()
         assert np.array_equal(m.density_array(), o.get_density_all()), f"mutate+condense, round {rnd}"

@@ -120,7 +120,7 @@ def test_steady_migration_py(oracle_mod, mods, gpu):
     extinctions = migrations = 0
     for it in range(5):
         m.generate(100); o.generate(100)
-        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        gpu.lib().eco_array_urand_seed(it); gpu.lib().eco_array_grand_reset(); m.mutate()
         O.srand(it); O.reset_grand(); o.mutate()
         mv = m.migrate()
         assert mv == o.migrate()
@@ -151,7 +151,7 @@ def test_sar_py_reuses_one_model_object(oracle_mod, mods, gpu, area, nsp, mut_ma
     o.set("fixMigration", 1); o.set("fixMutation", 1)
     for it in range(4):
         m.generate(100); o.generate(100)
-        O.srand(100 + it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        gpu.lib().eco_array_urand_seed(100 + it); gpu.lib().eco_array_grand_reset(); m.mutate()
         O.srand(100 + it); O.reset_grand(); o.mutate()
         assert m.migrate() == o.migrate()
         assert m.condense() == o.condense()
@@ -186,7 +186,7 @@ def test_panmictic_ecolab_py(oracle_mod, mods, gpu):
     o = load_oracle(O, p, np.array([m.density()], dtype=np.int32), None, scalars=_scalars_of(m))
     for it in range(6):
         m.generate(100); o.generate(100)
-        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        gpu.lib().eco_array_urand_seed(it); gpu.lib().eco_array_grand_reset(); m.mutate()
         O.srand(it); O.reset_grand(); o.mutate()
         assert m.condense() == o.condense()
         assert m.density() == o.get_density(0).tolist()
@@ -239,7 +239,7 @@ def test_fragmentation_pump_py(oracle_mod, mods, gpu):
     saved = None
     for it in range(6):
         m.generate(100); o.generate(100)
-        O.srand(it); gpu.lib().eco_array_grand_reset(); m.mutate()
+        gpu.lib().eco_array_urand_seed(it); gpu.lib().eco_array_grand_reset(); m.mutate()
         O.srand(it); O.reset_grand(); o.mutate()
         if it == 2:                                    # half epoch: fragment the landscape
             saved = m.migration()
