@@ -79,6 +79,7 @@ def main():
     nsp0 = len(m.species)
     if rank == 0:
         O.srand(123); O.reset_grand()
+        o.set("nprocs", world)   # species labels advance by nprocs per mutant (models/ecolab_model.cc:463-464)
         o.mutate()
         E.lib().eco_array_urand_seed(123); E.lib().eco_array_grand_reset()
     m.mutate()
