@@ -42,7 +42,14 @@ inline uint32_t round_up32(uint32_t n) { return (n + 31u) & ~31u; }
 // (the rest of the SM's 256 KB stays L1 and holds beta); failing that the widest that fits the SM twice, then once.
 uint32_t pick_tile_width(uint32_t cap) {
   for (uint32_t tw : {32u, 16u, 8u, 4u})
-    if (2 * (size_t)cap * tw * 4 <= 128 * 1024) return tw;
+    if (2 * (size_t)cap * tw * 4 <= 128 * 1024) {
+      // above 1024 species beta never fits beside the tiles and is read through L2 whatever L1 is left: take the next wider
+      // tile if two of them still fit the SM (1025-1784 species: 16 cells, 2049-3568: 8).  The narrow tiles are the slow ones
+      // (4 cells: 32 species rows per warp access, every gather a 16-byte piece of a different row) -- measured on the
+      // scripts' cadence at 64 x 64 cells, 1700-3300 species: generate(100) 20-26 ms with 4-cell tiles.
+      if (tw <= 8 && 2 * (size_t)cap * (2 * tw) * 4 + 4096 <= kSmemPerSm) return 2 * tw;
+      return tw;
+    }
   if (2 * ((size_t)cap * 16 + 64) + (size_t)cap + 1024 <= kSmemPerSm) return 4;
   if ((size_t)cap * 16 + (size_t)cap + 1024 <= kSmemPerSm) return 4;
   throw std::runtime_error("species count exceeds the shared-memory tile (nsp*16 B must fit in 227 KB)");

@@ -40,6 +40,7 @@ struct MigParams {
   unsigned int epoch;
   unsigned int* err;          // set to 1 if a flag wait timed out
   unsigned long long* total;
+  unsigned int* next_unit;    // walker: work-unit counter, zero at launch
 };
 
 // 2^52 + n as a double: pairing the int with a constant high word costs no arithmetic
@@ -206,15 +207,30 @@ __global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams
   const uint32_t lane = threadIdx.x & 31u, wpb = blockDim.x >> 5;
   const uint32_t rr = lane / QPR, q = lane % QPR;
   const uint32_t nrowblk = (L.nsp + RW - 1) / RW;
-  const unsigned long long nunits = (unsigned long long)p.nseg * L.ntx * nrowblk;
   const long long stride = (long long)L.row_stride;
   const bool first_q = q == 0, last_q = q == QPR - 1;
   unsigned long long acc = 0;
-  for (unsigned long long w = (unsigned long long)blockIdx.x * wpb + (threadIdx.x >> 5); w < nunits;
-       w += (unsigned long long)gridDim.x * wpb) {
-    const uint32_t b = (uint32_t)(w % nrowblk);
-    const uint32_t tx = (uint32_t)((w / nrowblk) % L.ntx);
-    const uint32_t seg = (uint32_t)(w / ((unsigned long long)nrowblk * L.ntx));
+  // Work units are handed out dynamically, tile column fastest: unit u = (segment, group of `wpb` consecutive species-row
+  // blocks, tile column) goes to the next free CTA, whose warps take one block each (a CTA reads wpb x 512 contiguous bytes per
+  // grid row).  The CTAs running at any time therefore work on ADJACENT tile columns of the same rows, started within a
+  // fraction of a microsecond of each other: the 32-byte sectors a warp reads from its neighbour tiles (one cell per
+  // species row and side) are lines the neighbour CTA is streaming through L2 at that moment.  With the static
+  // block-fastest order of round 1 a wave covered ~18 tile columns and drifted apart: at 4096 x 4096 x 1024 the kernel
+  // read 80-82 GB from DRAM for 68.7 GB of densities (ncu, profiles/r2_c4_traffic.csv).
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t ngr = (nrowblk + wpb - 1) / wpb;
+  const unsigned long long ncu = (unsigned long long)p.nseg * L.ntx * ngr;
+  __shared__ unsigned int s_unit;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_unit = atomicAdd(p.next_unit, 1u);
+    __syncthreads();
+    const unsigned long long w = s_unit;
+    if (w >= ncu) break;
+    const uint32_t tx = (uint32_t)(w % L.ntx);
+    const uint32_t b = (uint32_t)((w / L.ntx) % ngr) * wpb + warp;
+    const uint32_t seg = (uint32_t)(w / ((unsigned long long)ngr * L.ntx));
+    if (b >= nrowblk) continue;
     const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
     const uint32_t row = min(b * RW + rr, L.cap - 1);      // cap is a multiple of 32: the clamp never triggers, it bounds the address
     const double c = __ldg(p.cm + row);

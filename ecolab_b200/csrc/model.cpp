@@ -67,6 +67,10 @@ struct RunningClt {
     ++n;
     return (sum - .5 * n) * std::sqrt(12. / n);
   }
+  void skip() {   // advance the state past a draw nobody looks at (no sqrt, no division by n)
+    sum += urand01();
+    ++n;
+  }
 } g_grand;
 
 // host copy of the Philox4x32-10 contract (k_common.cuh), only for the `salt` getter:
@@ -325,9 +329,15 @@ struct eco_model {
       } else
         t[pos] = 0;
     }
-    std::vector<double> sc(t.size());
-    for (size_t i = 0; i < t.size(); ++i) sc[i] = t[i] != 0.0 ? range * gd : 0.0;
-    add_noise(t, sc);
+    // gspread with scale = (t != 0 ? range*gd : 0) (:351-358): the reference draws a gaussian for EVERY element of the dense
+    // temporary; the draws of the zero elements are multiplied by 0, so only the generator's state has to move past them
+    // (t + 0*z == t exactly: z is finite).  This loop is where ModelData::mutate spends its time -- two temporaries of
+    // nsp elements per mutant, a handful of them non-zero.
+    const double s = range * gd;
+    for (double& v : t) {
+      if (v != 0.0) v += s * g_grand.next();
+      else g_grand.skip();
+    }
   }
 
   // ModelData::mutate :362-470 -- one new species per entry of `parents`

@@ -22,6 +22,8 @@ SHAPES = [
     ((31, 1), 5, 0), ((1, 40), 12, 4),
     # long rows: the software-pipelined term loop (W >= 8) with every remainder, stream in shared memory and not
     (None, 50, 8), (None, 50, 9), ((5, 5), 80, 11), ((9, 2), 64, 12), ((20, 3), 200, 51), ((18, 2), 1100, 23),
+    # tile widths above 1024 species: 16 cells (<= 1784), 8 cells (<= 3568), 4 cells beyond
+    ((19, 2), 1700, 4), ((10, 3), 2100, 7), ((5, 2), 3700, 2),
 ]
 
 
