@@ -183,8 +183,7 @@ def build_model(E, args, nx, ny, comm, device, stream):
             getattr(m, k)(v)
     m.setGrid(nx, ny)
     m.seed(10)
-    for knob, val in (("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem), ("mig_variant", args.mig_variant),
-                      ("mig_stages", args.mig_stages), ("mig_rows", args.mig_rows), ("gen_dual", args.gen_dual)):
+    for knob, val in (("gen_stages", args.gen_stages), ("gen_nobsmem", args.gen_nobsmem), ("mig_rows", args.mig_rows), ("gen_dual", args.gen_dual)):
         if val:
             m.set_tuning(knob, val)
     m.fill_density_random(0, 199)   # mean 100, with gradients between neighbours so migrate really moves population
@@ -575,11 +574,9 @@ def main():
     ap.add_argument("--nsp", type=int, default=1024)
     ap.add_argument("--nnz", type=int, default=3)
     ap.add_argument("--e2e-n", type=int, default=0, dest="e2e_n", help="grid edge of the e2e leg (0 = the metric's grid where the host copy fits)")
-    ap.add_argument("--mig-stages", type=int, default=0, dest="mig_stages")
     ap.add_argument("--mig-rows", type=int, default=0, dest="mig_rows")
     ap.add_argument("--gen-stages", type=int, default=0, dest="gen_stages")
     ap.add_argument("--gen-nobsmem", type=int, default=0, dest="gen_nobsmem")
-    ap.add_argument("--mig-variant", type=int, default=0, dest="mig_variant")
     ap.add_argument("--gen-dual", type=int, default=0, dest="gen_dual")
     ap.add_argument("--e2e-unpipelined", action="store_true", dest="e2e_unpipelined")
     ap.add_argument("--no-cpu", action="store_true")

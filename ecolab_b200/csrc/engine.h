@@ -138,8 +138,6 @@ class Engine {
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory
   int gen_dual = 0;      // generate(1): two species-row blocks per consumer warp at a time; 0 / 1 = where applicable, -1 = off
-  int mig_variant = 0;   // 0 = automatic (tile-column pipeline where the tile width allows), 1 = register walker, 2 = pipeline
-  int mig_stages = 0;    // ring depth of the migrate pipeline; 0 = default
   int mig_rows = 0;      // grid rows per migrate work unit; 0 = automatic
   // dense (tensor-core) generate, k_dense.cuh.  gen_dense: 1 = use it, 0 / -1 = never (default: it is not bit-exact against
   // the reference's FP64 summation order, so the caller must ask for it).  dense_slices = P, the 8-bit slices beta is cut into (3: 2^-24 of the row maximum; 7: FP64).

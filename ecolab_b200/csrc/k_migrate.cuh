@@ -9,15 +9,10 @@
 // carrying, in registers, the current row's densities and its north fluxes.  Every density is loaded
 // from HBM exactly once and written once: 8 B of traffic per cell-species update.
 //
-// Two kernels share that arithmetic:
-//   migrate_pipe_kernel  (default, TW >= 8): a CTA walks down ONE tile column in lock-step.  A producer lane streams
-//                        the grid rows of the CTA's species-row group (16 KiB contiguous per grid row at 1024 species)
-//                        into a shared-memory ring with bulk (TMA-unit) copies; 16 consumer warps take their 512-byte
-//                        pieces out of the ring.  Bytes in flight are set by the ring depth, not by registers, and the
-//                        warps of a CTA cannot drift apart in y (round 1's walker showed 25.7-32 ms launch to launch
-//                        at C4 because they did).
-//   migrate_kernel       (fallback: TW = 4, i.e. more than 2048 species): each warp walks alone with five rows in
-//                        flight in registers.
+// One kernel: migrate_kernel, the register walker -- each warp walks down the grid rows of one block of species rows of one
+// tile column with five rows in flight in registers.  A tile-column pipeline through a shared-memory ring (bulk copies by a
+// producer lane, 16 consumer warps; round 2) was bit-exact but slower at every ring depth (C3: 2.5 vs 1.57 ms,
+// profiles/r2_variants.txt) and was removed.
 #pragma once
 #include "k_common.cuh"
 
@@ -30,11 +25,8 @@ struct MigParams {
   const int32_t* bottom_row;  // grid row y0+ny
   const double* cm;           // [cap] capped migration coefficient per species row (0 for padding rows)
   uint32_t yseg, nseg;        // grid rows per work unit, units along y
-  uint32_t gb, ngroups;       // pipe kernel: species-row blocks per unit, units per tile
-  uint32_t capblk;            // pipe kernel: cap / (species rows per warp-op)
-  uint32_t nstages;           // pipe kernel: ring depth (grid rows in flight per CTA)
   // multi-GPU, peer rows read over NVLink (null = ghost rows already filled): the neighbour ranks' "generate done"
-  // epoch counters; a boundary unit's producer waits until the counter reaches `epoch` before it copies the peer's row
+  // epoch counters; a boundary unit's warp waits until the counter reaches `epoch` before it copies the peer's row
   const unsigned int* top_flag;
   const unsigned int* bottom_flag;
   unsigned int epoch;
@@ -125,7 +117,7 @@ __device__ __forceinline__ void mig_finish(MigState& k, const int4 nv, int e, in
 }
 
 // =====================================================================================================================
-// fallback: the register walker.  A work unit = one block of species rows x one tile x n grid rows, streamed as the
+// the register walker.  A work unit = one block of species rows x one tile x n grid rows, streamed as the
 // sequence  north, row(0), ..., row(n-1), south  where `north` / `south` are the rows just outside the unit (ghost
 // rows or a peer GPU's boundary rows at the slab ends) or, at the edge of the GLOBAL grid, the unit's own first / last
 // row again (difference 0 -> flux 0).  NB rows are in flight per warp in registers; a row's load is re-issued the
@@ -256,175 +248,6 @@ __global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams
     const uint32_t rag = 1u + (x0 >= L.nx ? 0u : min(5u, L.nx - x0));
     if (ragged) mig_unit<DUALE, true, kMigRowsInFlight>(p0, pn, ps, dp, stride, n, eoff, eo_e, c, first_q, last_q, rag, acc);
     else mig_unit<DUALE, false, kMigRowsInFlight>(p0, pn, ps, dp, stride, n, eoff, eo_e, c, first_q, last_q, 0u, acc);
-  }
-#pragma unroll
-  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);
-  if (lane == 0 && acc) atomicAdd(p.total, acc);
-}
-
-// =====================================================================================================================
-// default: the tile-column pipeline.
-//   unit      = (y segment, tile column tx, group g of `gb` = NW*NS consecutive species-row blocks): per grid row the
-//               group is ONE contiguous piece of the tile, gb x 512 bytes;
-//   warp NW   = producer: one lane streams  north, row(0) .. row(n-1), south  of the unit into a ring of `nstages`
-//               shared-memory slots with one bulk copy per grid row ("full" mbarriers), re-filling a slot as soon as
-//               all consumer warps have released it ("empty" mbarriers); the ring runs on across unit boundaries;
-//   warps 0..NW-1 = consumers: warp w owns blocks g*gb + w*NS + {0..NS-1} for the whole walk, takes its 512-byte
-//               pieces of every row out of the ring and keeps the current row + north fluxes in registers; the
-//               extra cells across the tile boundary (one per species row and side) come straight from global memory,
-//               KE rows ahead; results go from registers to HBM as 16-byte streaming stores (512 B per warp-op).
-// Units are numbered group-fastest, then tile column, then segment, so the CTAs resident at one time cover adjacent
-// tile columns of the same rows: the extra-cell sectors they read from each other's tiles are L2 hits.
-// =====================================================================================================================
-constexpr int kMigPipeWarps = 16;     // consumer warps
-constexpr int kMigPipeEdge = 4;       // rows the extra-cell loads run ahead
-
-template <int TW, int NS, bool RAG>
-__device__ __forceinline__ void migp_unit(const MigParams& p, uint32_t tx, uint32_t g, uint32_t ys, uint32_t n, uint32_t warp,
-                                          uint32_t lane, uint32_t ring_s, uint32_t full_s, uint32_t empty_s, uint32_t stage_bytes,
-                                          uint32_t& stage, uint32_t& phase, unsigned long long& acc) {
-  constexpr int QPR = TW / 4, RW = 32 / QPR, KE = kMigPipeEdge;
-  const Layout& L = p.L;
-  const uint32_t rr = lane / QPR, q = lane % QPR;
-  const bool first_q = q == 0, last_q = q == QPR - 1;
-  const long long stride = (long long)L.row_stride;
-  const uint32_t x0 = tx * TW + 4 * q;
-  const uint32_t rag = 1u + (x0 >= L.nx ? 0u : min(5u, L.nx - x0));
-  long long eo_w, eo_e;
-  mig_edge_offsets(L, x0, TW, eo_w, eo_e);
-  const long long eoff = first_q ? eo_w : (last_q ? eo_e : 0);
-
-  bool valid[NS];
-  double c[NS];
-  const int32_t* ep[NS];   // this lane's extra cell of row(i + KE)
-  int32_t* dp[NS];
-  uint32_t soff[NS];
-  int e[NS][KE];
-#pragma unroll
-  for (int s = 0; s < NS; ++s) {
-    const uint32_t lb = warp * NS + s, blk = g * p.gb + lb;
-    valid[s] = blk < p.capblk;
-    const uint32_t row = min(blk * RW + rr, L.cap - 1);
-    c[s] = __ldg(p.cm + row);
-    const size_t lane_off = (size_t)tx * L.tile_stride + (size_t)row * TW + 4 * q;
-    const int32_t* p0 = L.base + (size_t)ys * L.row_stride + lane_off;
-    dp[s] = p.dst + (size_t)ys * L.row_stride + lane_off;
-    soff[s] = lb * 512u + lane * 16u;
-#pragma unroll
-    for (int j = 0; j < KE; ++j) e[s][j] = (valid[s] && (uint32_t)j < n) ? __ldg(p0 + eoff + (long long)j * stride) : 0;
-    ep[s] = p0 + eoff + (long long)KE * stride;
-  }
-
-  // one ring slot: wait until the row has landed, take this warp's pieces, release the slot
-  auto next_row = [&](int4 (&v)[NS]) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(full_s + 8u * stage), "r"(phase) : "memory");
-    const uint32_t a = ring_s + stage * stage_bytes;
-#pragma unroll
-    for (int s = 0; s < NS; ++s) {
-      v[s] = make_int4(0, 0, 0, 0);
-      if (valid[s])   // warp-uniform; a block past the species capacity has no bytes in the slot
-        asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v[s].x), "=r"(v[s].y), "=r"(v[s].z), "=r"(v[s].w) : "r"(a + soff[s]) : "memory");
-    }
-    __syncwarp();
-    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_s + 8u * stage) : "memory");
-    if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
-  };
-
-  int4 up[NS], cur[NS], nv[NS];
-  next_row(up);
-  next_row(cur);
-  MigState k[NS];
-#pragma unroll
-  for (int s = 0; s < NS; ++s) mig_start(k[s], up[s], cur[s], c[s]);
-
-  uint32_t i = 0;
-  for (; i + KE <= n; i += KE) {
-#pragma unroll
-    for (int j = 0; j < KE; ++j) {
-      next_row(nv);
-#pragma unroll
-      for (int s = 0; s < NS; ++s) {
-        if (valid[s]) {
-          const int ec = e[s][j];
-          if (i + j + KE < n) e[s][j] = __ldg(ep[s]);
-          mig_finish<false, RAG>(k[s], nv[s], ec, 0, c[s], first_q, last_q, rag, dp[s], acc);
-        }
-        ep[s] += stride;
-        dp[s] += stride;
-      }
-    }
-  }
-#pragma unroll 1
-  for (; i < n; ++i) {                                   // fewer than KE rows left: every extra cell is already in e[]
-    next_row(nv);
-#pragma unroll
-    for (int s = 0; s < NS; ++s) {
-      if (valid[s]) mig_finish<false, RAG>(k[s], nv[s], e[s][0], 0, c[s], first_q, last_q, rag, dp[s], acc);
-#pragma unroll
-      for (int j = 0; j + 1 < KE; ++j) e[s][j] = e[s][j + 1];
-      dp[s] += stride;
-    }
-  }
-}
-
-template <int TW, int NS>
-__global__ void __launch_bounds__((kMigPipeWarps + 1) * 32, 1) migrate_pipe_kernel(const MigParams p) {
-  extern __shared__ __align__(128) unsigned char mig_smem[];
-  constexpr int NW = kMigPipeWarps;
-  static_assert(TW >= 8, "one lane per species row needs the walker");
-  const Layout& L = p.L;
-  const uint32_t S = p.nstages, stage_bytes = p.gb * 512u;
-  uint64_t* full = reinterpret_cast<uint64_t*>(mig_smem + (size_t)S * stage_bytes);
-  uint64_t* empty = full + S;
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, NW); }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  const uint32_t per_seg = L.ntx * p.ngroups, nunits = p.nseg * per_seg;
-
-  if (warp == NW) {
-    if (lane == 0) {
-      uint32_t stage = 0, round = 0;
-      for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-        const uint32_t g = u % p.ngroups, tx = (u / p.ngroups) % L.ntx, seg = u / per_seg;
-        const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
-        const uint32_t bytes = min(p.gb, p.capblk - g * p.gb) * 512u;
-        const size_t off = (size_t)tx * L.tile_stride + (size_t)g * p.gb * 128u;            // a block is 128 ints of a tile
-        const int32_t* p0 = L.base + (size_t)ys * L.row_stride + off;
-        const bool peer_n = ys == 0 && L.y0 != 0, peer_s = ye == L.ny && L.y0 + ye < L.nyg;
-        const int32_t* pn = L.y0 + ys == 0 ? p0 : (ys == 0 ? p.top_row + off : p0 - (long long)L.row_stride);
-        const int32_t* ps = L.y0 + ye >= L.nyg ? p0 + (size_t)(n - 1) * L.row_stride
-                                               : (ye == L.ny ? p.bottom_row + off : p0 + (size_t)n * L.row_stride);
-        if (peer_n && p.top_flag) mig_wait_flag(p.top_flag, p.epoch, p.err);
-        if (peer_s && p.bottom_flag) mig_wait_flag(p.bottom_flag, p.epoch, p.err);
-        for (uint32_t i = 0; i < n + 2; ++i) {
-          const int32_t* src = i == 0 ? pn : (i == n + 1 ? ps : p0 + (size_t)(i - 1) * L.row_stride);
-          if (round) mbar_wait(empty + stage, (round - 1u) & 1u);
-          mbar_expect_tx(full + stage, bytes);
-          bulk_g2s(mig_smem + (size_t)stage * stage_bytes, src, bytes, full + stage);
-          if (++stage == S) { stage = 0; ++round; }
-        }
-      }
-    }
-    return;
-  }
-
-  const uint32_t ring_s = smem_u32(mig_smem), full_s = smem_u32(full), empty_s = smem_u32(empty);
-  uint32_t stage = 0, phase = 0;
-  unsigned long long acc = 0;
-  for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x) {
-    const uint32_t g = u % p.ngroups, tx = (u / p.ngroups) % L.ntx, seg = u / per_seg;
-    const uint32_t ys = seg * p.yseg, ye = min(L.ny, ys + p.yseg), n = ye - ys;
-    if ((tx + 1) * TW > L.nx) migp_unit<TW, NS, true>(p, tx, g, ys, n, warp, lane, ring_s, full_s, empty_s, stage_bytes, stage, phase, acc);
-    else migp_unit<TW, NS, false>(p, tx, g, ys, n, warp, lane, ring_s, full_s, empty_s, stage_bytes, stage, phase, acc);
   }
 #pragma unroll
   for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);

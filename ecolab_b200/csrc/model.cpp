@@ -1118,8 +1118,6 @@ int eco_set_tuning(eco_model* m, const char* knob, int value) {
   need(m);
   const std::string k(knob);
   if (k == "timing") { m->eng.reset_kernel_times(); m->eng.timing = value != 0; }
-  else if (k == "mig_variant") m->eng.mig_variant = value;
-  else if (k == "mig_stages") m->eng.mig_stages = value;
   else if (k == "mig_rows") m->eng.mig_rows = value;
   else if (k == "gen_stages") m->eng.gen_stages = value;
   else if (k == "gen_nobsmem") m->eng.gen_nobsmem = value;

@@ -113,16 +113,15 @@ def test_migrate_bit_exact_and_conserves(oracle_mod, gpu, grid, nsp, k):
 
 
 @pytest.mark.parametrize("grid,nsp,k", [((250, 3), 1000, 3), ((256, 4), 37, 3), ((120, 5), 300, 2), ((64, 7), 2000, 1), ((40, 70), 1000, 3),
-                                        ((33, 150), 64, 2), ((7, 41), 2100, 1)])
-@pytest.mark.parametrize("variant,stages", [(1, 0), (2, 2), (2, 5), (2, 12)])
-def test_migrate_kernels(oracle_mod, gpu, grid, nsp, k, variant, stages):
-    """migrate through the register walker (variant 1) and the tile-column pipeline (variant 2) at several ring depths:
-    same bits, ragged last tiles, partial species groups, many rows per unit and tile widths 32/16/8/4 included
-    (2100 species = 4-cell tiles: only the walker exists there and the knob falls back to it)."""
+                                        ((33, 150), 64, 2), ((7, 41), 2100, 1), ((6, 20), 3700, 1)])
+@pytest.mark.parametrize("rows", [0, 1, 7, 100000])
+def test_migrate_kernels(oracle_mod, gpu, grid, nsp, k, rows):
+    """migrate with the automatic unit length and with forced ones (1 row: every row is a unit boundary; 7; the whole
+    slab): same bits, ragged last tiles, partial species groups (fewer species-row blocks than warps in a CTA) and tile
+    widths 32/16/8/4 included.  Units are handed out dynamically, so the order they run in differs from launch to launch."""
     o, m, grid = pair(oracle_mod, gpu, grid, nsp, k, mig=0.11)
-    m.set_tuning("mig_variant", variant)
-    if stages:
-        m.set_tuning("mig_stages", stages)
+    if rows:
+        m.set_tuning("mig_rows", rows)
     for it in range(2):
         o.generate(1); m.generate(1)
         assert m.migrate() == o.migrate()
@@ -142,8 +141,8 @@ def test_migrate_extreme_densities(oracle_mod, gpu):
     d[rng.random(d.shape) < 0.1] = 2 ** 31 - 2
     o = load_oracle(oracle_mod, p, d, grid); m = load_gpu(gpu, p, d, grid)
     o.set("tstep", 1); m.tstep(1)            # dt = 1 since last_mig_tstep = 0
-    for variant in (0, 1, 2):
-        m.set_tuning("mig_variant", variant)
+    for rows in (0, 3, 0):
+        m.set_tuning("mig_rows", rows)
         before = m.species_totals()
         assert m.migrate() == o.migrate()
         got = m.density_array()
