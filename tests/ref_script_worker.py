@@ -42,6 +42,10 @@ def main():
     budgeted(ecolab_model.spatial_ecolab)
     budgeted(ecolab_model.panmictic_ecolab)
     os.environ.setdefault("ECOLAB_STEPS", "3")
+    # the scripts fill their parameter lists from Python's process-global random(), unseeded: give every rank of every run
+    # the same stream, or the 1-rank and the 2-rank run (and the two ranks of one run) start from different models
+    import random
+    random.seed(20251105)
     sys.argv = [script] + sys.argv[4:]
     try:
         runpy.run_path(script, run_name="__main__")
