@@ -90,7 +90,7 @@ Engine::~Engine() {
   cudaFree(d_boff_); cudaFree(d_stream_);
   cudaFree(d_aop_); cudaFree(d_bop_); cudaFree(d_dsp_); cudaFree(d_partial_); cudaFree(d_maxn_); cudaFree(dense_prof_);
   if (h_maxn_) cudaFreeHost(h_maxn_);
-  cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_scan_); cudaFree(d_stage_);
+  cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_scan_); cudaFree(d_stage_); cudaFree(d_scratch_);
   for (auto& p : d_band_) cudaFree(p);
   for (auto& e : ev_band_) if (e) cudaEventDestroy((cudaEvent_t)e);
   if (st_in_) cudaStreamDestroy((cudaStream_t)st_in_);

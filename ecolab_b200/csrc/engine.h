@@ -209,6 +209,8 @@ class Engine {
   MutRecord* d_rec_ = nullptr; size_t rec_cap_ = 0;
   uint32_t* d_scan_ = nullptr; size_t scan_cap_ = 0;   // mutate: per-cell event counts + scan block totals
   int32_t* d_stage_ = nullptr; size_t stage_cap_ = 0;  // cell-major staging
+  void* d_scratch_ = nullptr; size_t scratch_cap_ = 0;   // small per-call device temporaries (birth cells, species totals)
+  void* scratch(size_t bytes);
   int32_t* d_band_[4] = {nullptr, nullptr, nullptr, nullptr}; size_t band_cap_ = 0;   // step_host: 2 in + 2 out band stagings
   void* st_in_ = nullptr; void* st_out_ = nullptr;       // copy streams of step_host
   void* ev_band_[8] = {nullptr};

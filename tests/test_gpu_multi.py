@@ -27,8 +27,11 @@ def test_partitioned_model_matches_oracle(world, halo):
     import torch
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", str(_port()), os.path.join(HERE, "multi_gpu_worker.py")]
     env = dict(os.environ, ECOLAB_B200_HALO=halo)
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    for attempt in range(3):   # the free port found by _port() can be taken again before torchrun binds it
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+               "--master-port", str(_port()), os.path.join(HERE, "multi_gpu_worker.py")]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+        if "EADDRINUSE" not in r.stderr:
+            break
     assert r.returncode == 0 and f"MULTI_GPU_OK {world} {halo}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -93,7 +93,12 @@ def test_reference_script_unchanged_on_two_ranks(tmp_path, script, budget):
         else:
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                    "--master-port", str(_port()), worker, os.path.join(SCRIPTS, script), str(budget), out]
-        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(cwd))
+        for attempt in range(3):   # the free port found by _port() can be taken again before torchrun binds it
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(cwd))
+            if "EADDRINUSE" not in r.stderr:
+                break
+            if world > 1:
+                cmd[cmd.index("--master-port") + 1] = str(_port())
         assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
         outs.append(json.load(open(out)))
     a, b = outs
