@@ -29,7 +29,7 @@ import numpy as np
 
 from . import _cabi
 from ._cabi import EcolabError, MutRecord, check
-from .model import EcoList, EcolabModelBase, _Cell, _Member, _ptr
+from .model import _SCALARS_B, _SCALARS_F, EcoList, EcolabModelBase, _Cell, _Member, _ptr
 
 
 def slab_bounds(ny, world, rank):
@@ -224,6 +224,46 @@ class SpatialModel(EcolabModelBase):
         self._y0, self._y1 = 0, 1
         self._peer_version = None      # buf_version the neighbours' buffers were mapped for
         self._peer_failed = False
+        self._replica_dirty = False    # a ModelData member was assigned since the replicas were last made identical
+
+    # ---- replicated ModelData -----------------------------------------------------
+    # Every rank holds the whole ModelData and runs the same script, but not every assignment is rank-independent: the
+    # reference's scripts seed `array_urand` with 10+myid() ("different seed across processes", models/spatial_ecolab.py:14),
+    # so random_interaction() draws a different beta on every rank, and an unseeded Python random() differs too.  The
+    # reference makes the replicas identical again when SpatialModel::mutate broadcasts rank 0's ModelData (:262-263).  Here
+    # rank 0's parameters are broadcast before the first hot-path call that follows an assignment, so a partitioned run is
+    # the single-process run of the same script from the first generate on (tests/test_gpu_ref_scripts.py checks that).
+    def _set_array(self, name, kind, v):
+        super()._set_array(name, kind, v)
+        self._replica_dirty = True
+
+    def _set_scalar(self, name, v):
+        super()._set_scalar(name, v)
+        self._replica_dirty = True
+
+    def random_interaction(self, conn, sigma):
+        super().random_interaction(conn, sigma)
+        self._replica_dirty = True
+
+    def _sync_replicas(self):
+        if self.world == 1 or not self._replica_dirty:
+            return
+        self._replica_dirty = False
+        names = [(n, "f64") for n in self._TAILS_F64] + [(n, "u32") for n in self._TAILS_U32] + [("species", "i32")]
+        scal = _SCALARS_F + _SCALARS_B
+        blob = None
+        if self.rank == 0:
+            blob = {"arrays": {n: self._get_array(n, k) for n, k in names}, "scalars": {n: self._scalar(n) for n in scal}}
+        blob = self._comm.bcast_arrays(blob, src=0)
+        if self.rank != 0:
+            for n, k in names:
+                EcolabModelBase._set_array(self, n, k, blob["arrays"][n])
+            for n in scal:
+                EcolabModelBase._set_scalar(self, n, blob["scalars"][n])
+
+    def generate(self, niter=1):
+        self._sync_replicas()
+        super().generate(niter)
 
     # ---- distribution ------------------------------------------------------------
     def attach(self, comm):
@@ -500,11 +540,12 @@ class SpatialModel(EcolabModelBase):
         return t
 
     def append_tails(self, tails):
+        put = EcolabModelBase._set_array    # not an assignment by the script: the replicas stay marked identical
         for k in self._TAILS_F64:
-            self._set_array(k, "f64", np.concatenate([self._get_array(k, "f64"), tails[k]]))
+            put(self, k, "f64", np.concatenate([self._get_array(k, "f64"), tails[k]]))
         for k in self._TAILS_U32:
-            self._set_array(k, "u32", np.concatenate([self._get_array(k, "u32"), tails[k]]))
-        self._set_array("species", "i32", np.concatenate([self._get_array("species", "i32"), tails["species"]]))
+            put(self, k, "u32", np.concatenate([self._get_array(k, "u32"), tails[k]]))
+        put(self, "species", "i32", np.concatenate([self._get_array("species", "i32"), tails["species"]]))
 
     def append_species(self, cells):
         cells = np.ascontiguousarray(cells, dtype=np.uint32)
@@ -512,6 +553,7 @@ class SpatialModel(EcolabModelBase):
 
     # ---- the reflected methods ---------------------------------------------------------------
     def migrate(self, wait=True):
+        self._sync_replicas()
         if self.world == 1:
             t = C.c_uint64()
             check(self._L.eco_migrate(self._h, C.byref(t)))
@@ -543,6 +585,7 @@ class SpatialModel(EcolabModelBase):
         if self.world == 1:
             check(self._L.eco_step_host(self._h, _ptr(a), _ptr(b), a.shape[0], a.shape[1], int(niter), C.byref(t)))
             return t.value
+        self._sync_replicas()
         check(self._L.eco_step_host_begin(self._h, _ptr(a), a.shape[0], a.shape[1], int(niter)))
         ht = self.halo_tensors()
         if ht is not None:
@@ -554,9 +597,11 @@ class SpatialModel(EcolabModelBase):
     def condense(self):
         if self.world == 1:
             return super().condense()
+        self._sync_replicas()
         return dist_condense(self, self._comm)
 
     def mutate(self):
         if self.world == 1:
             return super().mutate()
+        self._sync_replicas()
         dist_mutate(self, self._comm)

@@ -70,7 +70,7 @@ def main():
         dens, ns_all = np.array([m.density()], dtype=np.int32), [m.nsp()]
     h = lambda a: hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()   # noqa: E731
     fp = {"generates": calls["n"], "tstep": int(m.tstep()), "nsp": len(m.species), "species": h(np.array(m.species(), dtype=np.int64)),
-          "density": h(dens.astype(np.int64)), "individuals": int(dens.sum()), "nsp_per_cell": list(map(int, ns_all)),
+          "species_unique": len(set(m.species())) == len(m.species), "density": h(dens.astype(np.int64)), "individuals": int(dens.sum()), "nsp_per_cell": list(map(int, ns_all)),
           "repro_rate": h(np.array(m.repro_rate())), "val": h(np.array(m.interaction.val())), "world": world,
           "halo": "peer" if spatial and world > 1 and int(m._scalar("peer_connected")) else "-"}
     if rank == 0:

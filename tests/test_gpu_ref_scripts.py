@@ -102,6 +102,9 @@ def test_reference_script_unchanged_on_two_ranks(tmp_path, script, budget):
         assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
         outs.append(json.load(open(out)))
     a, b = outs
-    for k in ("generates", "tstep", "nsp", "species", "density", "individuals", "nsp_per_cell", "repro_rate", "val"):
+    # everything but the species LABELS: a new species is labelled sp_cntr + k*nprocs (models/ecolab_model.cc:463-464), so the
+    # labels of a 2-rank run advance twice as fast -- by the reference's own rule; they must still be unique
+    for k in ("generates", "tstep", "nsp", "density", "individuals", "nsp_per_cell", "repro_rate", "val"):
         assert a[k] == b[k], (k, a[k], b[k])
+    assert a["species_unique"] and b["species_unique"]
     assert b["world"] == 2
