@@ -643,6 +643,8 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "numY") *out = (double)m->numY;
   else if (s == "maxNbrs") *out = (double)m->maxNbrs;
   else if (s == "launches") *out = (double)m->eng.launches();
+  else if (s == "last_block") { int g, b, sm; m->eng.last_kernel_config(&g, &b, &sm); *out = (double)b; }   // threads per CTA of the last hot kernel
+  else if (s == "last_smem") { int g, b, sm; m->eng.last_kernel_config(&g, &b, &sm); *out = (double)sm; }
   else if (s == "device_bytes") *out = (double)m->eng.bytes_allocated();
   else if (s == "dense_active") *out = m->eng.dense_wanted() ? 1.0 : 0.0;
   else if (s == "dense_q") *out = (double)m->eng.dense_last_q();
