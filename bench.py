@@ -274,7 +274,8 @@ def run_native(args):
     if not args.no_verify:
         verify = verify_leg(m, args, nx, ny, world, rank)
 
-    del m   # frees the device buffers before the next leg allocates its own
+    m.close()   # frees the device buffers before the next leg allocates its own
+    del m
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region, bounded grid ----
     e2e = None
     if not args.no_e2e:
@@ -356,7 +357,7 @@ def extra_legs(E, args, local, stream):
         g, mg = kt["generate"][0] / 5, kt["migrate"][0] / 5
         sweep[str(nnz)] = {"generate_ms": g, "migrate_ms": mg, "updates_per_s": 2 ** 30 / ((g + mg) * 1e-3),
                            "generate_hbm_frac": 8.0 * 2 ** 30 / (g * 1e-3) / 1e9 / peaks()[0]}
-        del m
+        m.close(); del m
     out["nnz_sweep_c3"] = {"workload": "spatial 1024x1024 cells x 1024 species, generate(1)+migrate(), 5 steps", "by_nnz_per_row": sweep}
     # the scripts' cadence (models/spatial_ecolab.py:66-78) at BASELINE.json config 2's shape
     a = copy.copy(args); a.nsp = 1000; a.nnz = 3
@@ -376,7 +377,7 @@ def extra_legs(E, args, local, stream):
             torch.cuda.synchronize()
             walls.append(time.perf_counter() - t0); dev.append(e0.elapsed_time(e1) * 1e-3); nsps.append(len(m.species))
         if rep == 0:
-            del m
+            m.close(); del m
     upd = 64 * 64 * 1000 * 100
     out["cadence_c2"] = {"workload": "spatial 64x64 cells x 1000 species (3 nnz/row, mutation = mut_max = 1e-5, the scripts' parameters): "
                                      "generate(100)+mutate()+migrate()+condense() per round",
@@ -384,7 +385,7 @@ def extra_legs(E, args, local, stream):
                          "species_after_round": nsps,
                          "generation_updates_per_s": upd / float(np.median(walls)),
                          "non_generate_share": 1.0 - float(np.median(dev)) / float(np.median(walls))}
-    del m
+    m.close(); del m
     if not args.no_dense:
         try:
             out["dense_c5"] = dense_leg(E, args, local, stream, steps=3, warmup=2)
@@ -394,22 +395,27 @@ def extra_legs(E, args, local, stream):
 
 
 def e2e_grid(args, world):
-    """The grid of the e2e leg: the metric's own (C4) when its host copy, split over the ranks, stays within 32 GiB of
-    pinned memory per rank and 35 % of the box's available RAM in total; else the largest square power-of-two grid that does."""
-    if args.e2e_n:
-        return args.e2e_n
+    """The grid of the e2e leg and whether the step runs IN PLACE (one pinned host buffer is both input and output: the
+    banded pipeline writes band k-1 back after band k has been read).  The metric's own grid (C4) when one host copy of it,
+    split over the ranks, stays within 64 GiB of pinned memory per rank and 40 % of the box's available RAM in total; else
+    the largest square power-of-two grid whose separate input and output copies stay within 32 GiB per rank and 35 %."""
     try:
         import psutil
         avail = psutil.virtual_memory().available
     except Exception:   # noqa: BLE001
         avail = 64 << 30
+    if args.e2e_n:
+        return args.e2e_n, False
+    one = 4096 * 4096 * args.nsp * 4
+    if one / world <= (64 << 30) and one <= 0.40 * avail and not args.e2e_unpipelined:
+        return 4096, True
     n = 4096
     while n > 256:
         total = 2 * n * n * args.nsp * 4          # in + out
         if total / world <= (32 << 30) and total <= 0.35 * avail:
             break
         n //= 2
-    return n
+    return n, False
 
 
 def e2e_leg(E, args, comm, local, stream, world, rank):
@@ -418,11 +424,12 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     bands of grid rows; under torch.distributed every rank streams its own slab over its own PCIe link."""
     import torch
     import torch.distributed as dist
-    nx = ny = e2e_grid(args, world)
+    n, inplace = e2e_grid(args, world)
+    nx = ny = n
     m = build_model(E, args, nx, ny, comm, local, stream)
     nloc = (m._y1 - m._y0) * nx
     host_in = torch.empty((nloc, args.nsp), dtype=torch.int32, pin_memory=True)
-    host_out = torch.empty((nloc, args.nsp), dtype=torch.int32, pin_memory=True)
+    host_out = host_in if inplace else torch.empty((nloc, args.nsp), dtype=torch.int32, pin_memory=True)
     a_in, a_out = host_in.numpy(), host_out.numpy()
     block = np.random.default_rng(5 + rank).integers(0, 200, size=(min(nloc, 16384), args.nsp), dtype=np.int32)
     for i in range(0, nloc, len(block)):          # synthetic state, mean 100, tiled from one random block
@@ -442,7 +449,7 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    steps = max(2, min(args.steps, 4))
+    steps = 2 if inplace else max(2, min(args.steps, 4))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(steps):
@@ -456,9 +463,10 @@ def e2e_leg(E, args, comm, local, stream, world, rank):
         ms = float(t.item())
     assert int(a_out[:1024].sum()) > 0
     val = nx * ny * args.nsp * steps / (ms * 1e-3)
-    del m
+    m.close(); del m
     return {"value": val, "unit": UNIT, "h2d_bytes_per_step": int(nx * ny * args.nsp * 4), "d2h_bytes_per_step": int(nx * ny * args.nsp * 4 + 8 * world),
-            "workload": f"spatial {nx}x{ny} cells x {args.nsp} species through pinned host buffers, {world} row slab(s), "
+            "workload": f"spatial {nx}x{ny} cells x {args.nsp} species through pinned host buffers"
+                        f"{' (in place: one buffer is input and output)' if inplace else ''}, {world} row slab(s), "
                         f"{nloc * args.nsp * 4 / 2**30:.1f} GiB per rank each way per step", "steps": steps, "ms_per_step": ms / steps,
             "call": "eco_step_host (row-banded H2D/kernel/D2H pipeline; partitioned: eco_step_host_begin + halo + eco_step_host)"
                     if not args.e2e_unpipelined else "eco_set_density_all + eco_step + eco_get_density_all"}
@@ -544,7 +552,7 @@ def dense_leg(E, args, local, stream, steps, warmup, sparse_too=False):
     if args.dense_prof:
         names = ("mma_wait_tmem_empty", "mma_wait_smem_full", "mma_issue", "tiles", "epi_wait_tmem_full", "epi_work")
         roofline["cta0_cycles_last_launch"] = {n: int(m._scalar(f"dense_prof{i}")) for i, n in enumerate(names)}
-    del m
+    m.close(); del m
     return {"metric": METRIC, "value": updates * steps / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": steps,
             "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "s8 x u8 -> s32 slices, f64 epilogue -> i32", "data": "synthetic",

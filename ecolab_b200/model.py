@@ -139,11 +139,16 @@ class EcolabModelBase:
         for n in _SCALARS_B:
             setattr(self, n, self._scalar_member(n, bool))
 
+    def close(self):
+        """Destroy the C++ model now (device buffers included).  The members are closures over `self`, so the object sits in
+        a reference cycle and `del m` alone frees the device memory only at the next garbage collection."""
+        if getattr(self, "_h", None):
+            self._L.eco_destroy(self._h)
+            self._h = None
+
     def __del__(self):
         try:
-            if self._h:
-                self._L.eco_destroy(self._h)
-                self._h = None
+            self.close()
         except Exception:
             pass
 
