@@ -178,7 +178,7 @@ class Engine {
   const unsigned int* peer_flag_[2] = {nullptr, nullptr};
   void* peer_map_[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // opened IPC mappings per side
   bool peer_open_[2] = {false, false};
-  unsigned int* d_flags_ = nullptr;      // [0] epoch published by this rank, [2] error word; IPC-exported
+  unsigned int* d_flags_ = nullptr;      // [0] epoch published by this rank, [2] migrate's peer-wait error word, [3] the dense kernel's watchdog word; IPC-exported
   unsigned int gen_epoch_ = 0;
   uint64_t buf_version_ = 0;
 

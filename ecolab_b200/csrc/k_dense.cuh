@@ -53,6 +53,7 @@ struct DenseParams {
   const double* rr;            // [mtiles*128] repro_rate
   const double* rscale;        // [mtiles*128] 2^-s_i
   double* partial;             // [ntn][mtiles][128 cols][128 rows] running sums between group rounds, or null
+  unsigned int* err;           // watchdog word: set when a wait made no progress for ~10 s (checked by the host)
   unsigned long long* prof;    // optional [grid][8] cycle counters (tools only): MMA warp waits / issue, epilogue wait / work
   double* xout;                // cell-major [cell][nsp] pre-rounding x (diagnostic), or null
   uint32_t P, Q;               // slices of beta / of the densities
@@ -102,8 +103,10 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int (&v)[8]) {
       : "memory");
 }
 
-// mbarrier wait with a watchdog: a mis-programmed pipeline traps instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
+// mbarrier wait with a watchdog: a pipeline that stops making progress raises an error word instead of hanging the GPU (or
+// trapping, which would kill the context under a debugger or time-slicing).  Once the word is set every wait of the launch
+// returns at once, the kernel runs out, and the host finds the word at its next synchronisation and throws.
+__device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity, unsigned int* err) {
   uint32_t done = 0;
   const long long t0 = clock64();
   for (uint32_t spin = 0;; ++spin) {
@@ -112,7 +115,10 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
                  : "r"(smem_u32(bar)), "r"(parity)
                  : "memory");
     if (done) return;
-    if ((spin & 1023u) == 1023u && clock64() - t0 > 8000000000ll) __trap();   // ~4 s
+    if ((spin & 1023u) == 1023u) {
+      if (*reinterpret_cast<volatile unsigned int*>(err)) return;
+      if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); return; }   // ~10 s without progress
+    }
   }
 }
 
@@ -240,7 +246,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
         const uint8_t* a = p.aop + (size_t)mt * p.nkc * a_bytes;
         const uint8_t* b = p.bop + (size_t)nt * p.nkc * b_bytes;
         for (uint32_t kc = 0; kc < p.nkc; ++kc) {
-          if (round) mbar_wait_wd(s_empty + stage, (round - 1u) & 1u);
+          if (round) mbar_wait_wd(s_empty + stage, (round - 1u) & 1u, p.err);
           unsigned char* dst = dense_smem + (size_t)stage * stage_bytes;
           mbar_expect_tx(s_full + stage, stage_bytes);
           bulk_g2s(dst, a + (size_t)kc * a_bytes, a_bytes, s_full + stage);
@@ -260,13 +266,13 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
         uint32_t mt, nt;
         if (!dense_tile(p, id, mt, nt)) continue;
         long long c0 = clock64();
-        if (k) mbar_wait_wd(&s_tempty, (k - 1u) & 1u);   // the epilogue has drained the accumulators of the previous tile
+        if (k) mbar_wait_wd(&s_tempty, (k - 1u) & 1u, p.err);   // the epilogue has drained the accumulators of the previous tile
         tc_fence_after();
         pc[0] += clock64() - c0;
         uint32_t written = 0;                             // groups that already hold a partial sum of this tile
         for (uint32_t kc = 0; kc < p.nkc; ++kc) {
           c0 = clock64();
-          mbar_wait_wd(s_full + stage, round & 1u);
+          mbar_wait_wd(s_full + stage, round & 1u, p.err);
           tc_fence_after();
           const long long c1 = clock64();
           pc[1] += c1 - c0;
@@ -336,7 +342,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
         advance(cp);
       }
       const long long e0 = clock64();
-      mbar_wait_wd(&s_tfull, k & 1u);
+      mbar_wait_wd(&s_tfull, k & 1u, p.err);
       tc_fence_after();
       const long long e1 = clock64();
       ew += e1 - e0;
