@@ -5,6 +5,7 @@
 // arrays, parameter mutation) is O(nsp + nnz) serial host work exactly as in the
 // reference; everything O(cells x species) runs in engine.cu on the GPU.
 #include <algorithm>
+#include <iterator>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -311,17 +312,18 @@ struct eco_model {
     return condense_apply(mask);
   }
 
-  // do_row_or_col, models/ecolab_model.cc:327-359
-  void perturb_links(std::vector<double>& t, double range, double minval, double gd) {
+  // do_row_or_col, models/ecolab_model.cc:327-359, on the first L elements of the dense temporary `t`; appends to `nz` the
+  // (ascending) indices that held a link when the gaussians were applied -- the only elements later steps can find non-zero
+  void perturb_links(std::vector<double>& t, size_t L, double range, double minval, double gd, std::vector<uint32_t>& nz) {
     double r = (2.0 * g_urand.next()) / kRandMax - 1 + gen_bias;
     r = r > 0 ? r / (1 + gen_bias) : r / (1 - gen_bias);
-    size_t cnt = t.size();
+    size_t cnt = L;
     if (r != 0) {
       const double inv = 1 / std::fabs(r);
       if (inv < 2147483648.0) cnt = (size_t)(unsigned)((int)inv - 1);
     }
-    cnt = std::min(cnt, t.size());
-    const double span = (double)(t.size() - 1);
+    cnt = std::min(cnt, L);
+    const double span = (double)(L - 1);
     for (size_t j = 0; j < cnt; ++j) {
       const int pos = (int)(span * ((double)g_urand.next() / kRandMax) + .5);
       if (r > 0) {
@@ -332,11 +334,27 @@ struct eco_model {
     // gspread with scale = (t != 0 ? range*gd : 0) (:351-358): the reference draws a gaussian for EVERY element of the dense
     // temporary; the draws of the zero elements are multiplied by 0, so only the generator's state has to move past them
     // (t + 0*z == t exactly: z is finite).  This loop is where ModelData::mutate spends its time -- two temporaries of
-    // nsp elements per mutant, a handful of them non-zero.
+    // nsp elements per mutant, a handful of them non-zero.  The uniforms are drawn a block at a time (the divisions by
+    // RAND_MAX pipeline instead of sitting between two steps of the running sum); the sum itself stays one addition after
+    // the other, in draw order: it is not associative.
     const double s = range * gd;
-    for (double& v : t) {
-      if (v != 0.0) v += s * g_grand.next();
-      else g_grand.skip();
+    double u[64];
+    for (size_t i0 = 0; i0 < L; i0 += 64) {
+      const size_t nb = std::min<size_t>(64, L - i0);
+      for (size_t k = 0; k < nb; ++k) u[k] = urand01();
+      double sum = g_grand.sum;
+      unsigned n = g_grand.n;
+      for (size_t k = 0; k < nb; ++k) {
+        sum += u[k];
+        ++n;
+        double& v = t[i0 + k];
+        if (v != 0.0) {
+          v += s * ((sum - .5 * n) * std::sqrt(12. / n));
+          nz.push_back((uint32_t)(i0 + k));
+        }
+      }
+      g_grand.sum = sum;
+      g_grand.n = n;
     }
   }
 
@@ -378,44 +396,59 @@ struct eco_model {
     const double range = odiag_max - odiag_min;
     // entries of every row / column in COO order (the reference scans the whole COO per mutant, :414-423; the lists give
     // the same scatter order -- a later duplicate overwrites an earlier one -- in O(row length)); entries appended by an
-    // earlier mutant of this batch are seen by a later one, as in the reference
+    // earlier mutant of this batch are seen by a later one, as in the reference.
+    // The reference's dense temporaries of nsp+i elements per mutant are kept (the gaussians are drawn per ELEMENT), but
+    // everything after the draws walks only the elements that can be non-zero: the ascending union of the two index lists
+    // perturb_links returns -- the same elements, in the same order, as the reference's dense loops meet them.
     std::vector<std::vector<uint32_t>> byrow(n0 + m), bycol(n0 + m);
     for (size_t j = 0; j < row.size(); ++j) { byrow[row[j]].push_back((uint32_t)j); bycol[col[j]].push_back((uint32_t)j); }
+    std::vector<double> rw(n0 + m, 0.0), cl(n0 + m, 0.0);
+    std::vector<uint32_t> nzr, nzc, both;
     for (size_t i = 0; i < m; ++i) {
       const size_t L = n0 + i;   // index of the new species; length of the dense temporaries (:411)
       const uint32_t p = parents[i];
-      std::vector<double> rw(L, 0.0), cl(L, 0.0);
+      nzr.clear(); nzc.clear(); both.clear();
       for (uint32_t j : byrow[p]) if (col[j] < L) rw[col[j]] = val[j];
       rw[p] = diag[p];
-      perturb_links(rw, range, odiag_min, gd[i]);
+      perturb_links(rw, L, range, odiag_min, gd[i], nzr);
       for (uint32_t j : bycol[p]) if (row[j] < L) cl[row[j]] = val[j];
       cl[p] = diag[p];
-      perturb_links(cl, range, odiag_min, gd[i]);
+      perturb_links(cl, L, range, odiag_min, gd[i], nzc);
+      std::set_union(nzr.begin(), nzr.end(), nzc.begin(), nzc.end(), std::back_inserter(both));
 
       // keep n.beta.n < 0: shave the positive part (:434-446); note diag is indexed by i, as in the reference (:437)
       double s = 0;
-      std::vector<uint8_t> pos(L);
-      for (size_t q = 0; q < L; ++q) { pos[q] = rw[q] + cl[q] > 0; if (pos[q]) s += rw[q] + cl[q]; }
+      int nadj = 0;
+      for (uint32_t q : both)
+        if (rw[q] + cl[q] > 0) {
+          s += rw[q] + cl[q];
+          nadj += (rw[q] != 0.0 || cl[q] != 0.0);
+        }
       s += diag[i];
       if (s > 0) {
-        int nadj = 0;
-        for (size_t q = 0; q < L; ++q) nadj += pos[q] && (rw[q] != 0.0 || cl[q] != 0.0);
-        for (size_t q = 0; q < L; ++q) {
-          const bool a = pos[q] && rw[q] != 0.0, b = pos[q] && cl[q] != 0.0;
+        for (uint32_t q : both) {
+          const bool pos = rw[q] + cl[q] > 0;
+          const bool a = pos && rw[q] != 0.0, b = pos && cl[q] != 0.0;
           if (a) rw[q] = rw[q] - s / nadj;
           if (b) cl[q] = cl[q] - s / nadj;
         }
       }
-      for (size_t q = 0; q < L; ++q)
+      for (uint32_t q : nzr)
         if (rw[q] != 0.0) {
           byrow[L].push_back((uint32_t)val.size()); bycol[q].push_back((uint32_t)val.size());
           val.push_back(rw[q]); row.push_back((uint32_t)L); col.push_back((uint32_t)q);
         }
-      for (size_t q = 0; q < L; ++q)
+      for (uint32_t q : nzc)
         if (cl[q] != 0.0) {
           byrow[q].push_back((uint32_t)val.size()); bycol[L].push_back((uint32_t)val.size());
           val.push_back(cl[q]); row.push_back((uint32_t)q); col.push_back((uint32_t)L);
         }
+      // back to all-zero for the next mutant: everything that was written is in the scatter lists or in nzr / nzc
+      for (uint32_t j : byrow[p]) if (col[j] < rw.size()) rw[col[j]] = 0.0;
+      for (uint32_t j : bycol[p]) if (row[j] < cl.size()) cl[row[j]] = 0.0;
+      rw[p] = 0.0; cl[p] = 0.0;
+      for (uint32_t q : nzr) rw[q] = 0.0;
+      for (uint32_t q : nzc) cl[q] = 0.0;
     }
     for (size_t k = 0; k < m; ++k) { create.push_back(0); species.push_back((int32_t)(k * nprocs) + sp_cntr); }
     sp_cntr += (int)(m * nprocs);
