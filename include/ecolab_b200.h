@@ -190,8 +190,8 @@ void eco_array_urand_seed(int seed);
 void eco_array_grand_reset(void);
 
 /* tuning / profiling knobs (0 = automatic): "gen_dual" (-1: one species-row block per consumer warp of generate(1)),
- * "gen_stages", "gen_nobsmem" (1: beta through L1/L2 even where it fits in shared memory), "mig_variant" (1 = register
- * walker, 2 = tile-column pipeline), "mig_stages" (ring depth of the migrate pipeline), "gen_dense" (1 = tensor-core
+ * "gen_stages", "gen_nobsmem" (1: beta through L1/L2 even where it fits in shared memory), "mig_rows" (grid rows per work
+ * unit of migrate), "gen_dense" (1 = tensor-core
  * generate for dense beta; never automatic), "dense_slices", "timing" (1 = record a CUDA-event pair around every
  * generate/migrate launch, 0 = off and reset) */
 int eco_set_tuning(eco_model* m, const char* knob, int value);
