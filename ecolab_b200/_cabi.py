@@ -74,6 +74,7 @@ SIGNATURES = {
     "eco_restart": [_vp, _cp],
     "eco_migrate_local": [_vp, _P(_u64)],
     "eco_migrate_local_async": [_vp, _P(_vp)],
+    "eco_alive_mask_device": [_vp, _P(_vp), _sz],
     "eco_halo_ptrs": [_vp, _P(_vp), _P(_vp), _P(_vp), _P(_vp), _P(_sz)],
     "eco_peer_export": [_vp, _vp, _sz],
     "eco_peer_connect": [_vp, _vp, _vp],

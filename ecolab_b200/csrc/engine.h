@@ -83,6 +83,7 @@ class Engine {
   void step_host_begin(const int32_t* in_host, uint32_t niter, uint64_t t0, uint32_t seed);
   // alive[s] = 1 iff some owned cell has density != 0
   void alive_mask(uint8_t* alive_host);
+  uint8_t* alive_mask_device();                        // the same, left on the device (stream-ordered)
   // compact species rows: keep[s] != 0 survives, order preserved
   void compact_species(const uint8_t* keep_host, uint32_t nkeep);
   // speciation: k = ROUND(ms[s] * n), n -= k; returns records sorted by (cell, slot); cell ids GLOBAL

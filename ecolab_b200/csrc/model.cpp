@@ -1106,6 +1106,14 @@ int eco_alive_mask(eco_model* m, uint8_t* alive, size_t nsp) {
   if (nsp) m->eng.alive_mask(alive);
   ECO_CATCH
 }
+int eco_alive_mask_device(eco_model* m, void** mask_dev, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (!mask_dev) throw std::runtime_error("alive_mask_device: null output");
+  if (nsp != m->nsp() || nsp != m->eng.nsp()) throw std::runtime_error("alive_mask_device: species count differs from the model");
+  *mask_dev = nsp ? m->eng.alive_mask_device() : nullptr;
+  ECO_CATCH
+}
 int eco_condense_apply(eco_model* m, const uint8_t* alive, size_t nsp, unsigned* removed) {
   ECO_TRY
   need(m);

@@ -98,10 +98,44 @@ class Comm:
         return [o.cpu().numpy().view(np.uint32)[:c] for o, c in zip(outs, counts)]
 
     def bcast_arrays(self, arrays, src=0):
-        """Broadcast a dict of numpy arrays from `src` (shapes first, then one flat buffer per dtype)."""
+        """Broadcast a (possibly nested) dict of numpy arrays / scalars from `src` as an object (setup-time replica
+        synchronisation: sizes are not known on the receivers)."""
         obj = [arrays if self.rank == src else None]
         self.dist.broadcast_object_list(obj, src=src, group=self.group)
         return obj[0]
+
+    def bcast_tails(self, tails, f64_keys, u32_keys, src=0):
+        """Broadcast the arrays appended by ModelData::mutate (a dict name -> 1-D array, plus "species" int32) from `src`
+        as three tensors: one int64 header with the lengths, one float64 buffer, one int32 buffer -- no pickling, and on
+        NCCL nothing but the header is read before the payload is on every device."""
+        keys = list(f64_keys) + list(u32_keys) + ["species"]
+        hdr = self._t(np.array([len(tails[k]) for k in keys] if self.rank == src else [0] * len(keys), dtype=np.int64))
+        self.dist.broadcast(hdr, src=src, group=self.group)
+        lens = [int(v) for v in hdr.cpu().numpy()]
+        nf, ni = sum(lens[: len(f64_keys)]), sum(lens[len(f64_keys):])
+        if self.rank == src:
+            fb = np.concatenate([np.asarray(tails[k], dtype=np.float64) for k in f64_keys]) if nf else np.zeros(0)
+            ib = np.concatenate([np.asarray(tails[k]).astype(np.uint32).view(np.int32) for k in u32_keys] +
+                                [np.asarray(tails["species"], dtype=np.int32)]) if ni else np.zeros(0, dtype=np.int32)
+        else:
+            fb, ib = np.zeros(nf, dtype=np.float64), np.zeros(ni, dtype=np.int32)
+        tf, ti = self._t(fb), self._t(ib)
+        if nf:
+            self.dist.broadcast(tf, src=src, group=self.group)
+        if ni:
+            self.dist.broadcast(ti, src=src, group=self.group)
+        if self.rank == src:
+            return tails
+        fb, ib = tf.cpu().numpy(), ti.cpu().numpy()
+        out, of, oi = {}, 0, 0
+        for k, n in zip(keys, lens):
+            if k in f64_keys:
+                out[k] = fb[of:of + n].copy(); of += n
+            elif k == "species":
+                out[k] = ib[oi:oi + n].copy(); oi += n
+            else:
+                out[k] = ib[oi:oi + n].view(np.uint32).copy(); oi += n
+        return out
 
     def sendrecv_rows(self, send_up, recv_up, send_down, recv_down):
         """Exchange boundary rows with rank-1 ("up", lower y) and rank+1 ("down").  Tensors alias device memory."""
@@ -143,7 +177,13 @@ def dist_migrate(ops, comm, wait=True):
 
 
 def dist_condense(ops, comm):
-    """SpatialModel::condense (:171-196): local mask, logical-or all-reduce, identical compaction everywhere."""
+    """SpatialModel::condense (:171-196): local mask, logical-or all-reduce, identical compaction everywhere.  On GPUs the
+    mask never leaves the device before the collective: the all-reduce runs in place on the kernel's output and the reduced
+    mask is read once (ModelData::condense needs it on the host)."""
+    dev = ops.alive_mask_device() if comm.backend == "nccl" and hasattr(ops, "alive_mask_device") else None
+    if dev is not None:
+        comm.dist.all_reduce(dev, op=comm.dist.ReduceOp.MAX, group=comm.group)
+        return ops.condense_apply(np.ascontiguousarray(dev.cpu().numpy()))
     mask = np.ascontiguousarray(comm.allreduce_max_u8(ops.alive_mask()))
     return ops.condense_apply(mask)
 
@@ -160,7 +200,7 @@ def dist_mutate(ops, comm):
     if comm.rank == 0:   # ModelData::mutate on rank 0 only (:251-258): it draws from rank 0's libc stream
         ops.mutate_model(parents)
         tails = ops.tails(before)
-    tails = comm.bcast_arrays(tails, src=0)
+    tails = comm.bcast_tails(tails, ops._TAILS_F64, ops._TAILS_U32, src=0)
     if comm.rank != 0:
         ops.append_tails(tails)
     ops.append_species(cells)
@@ -509,6 +549,17 @@ class SpatialModel(EcolabModelBase):
         if ns:
             check(self._L.eco_alive_mask(self._h, _ptr(mask), ns))
         return mask
+
+    def alive_mask_device(self):
+        """The alive mask left on the device as a uint8 torch tensor aliasing the engine's buffer, or None when the kernels
+        do not run on torch's current stream (the caller then uses alive_mask)."""
+        import torch
+        ns = int(self._scalar("nsp"))
+        if not ns or not self._on_torch_stream():
+            return None
+        p = C.c_void_p()
+        check(self._L.eco_alive_mask_device(self._h, C.byref(p), ns))
+        return torch.as_tensor(_DevMem(p.value, ns, "|u1"), device=torch.device("cuda", self._device))
 
     def condense_apply(self, mask):
         r = C.c_uint()

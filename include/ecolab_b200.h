@@ -158,6 +158,10 @@ int eco_migrate_local(eco_model* m, uint64_t* abs_delta_sum);
  * stream after the launch), so the all-reduce of SpatialModel::migrate's return value (:667-672) can be enqueued
  * behind the kernel without a host round trip */
 int eco_migrate_local_async(eco_model* m, void** total_dev);
+/* alive mask of eco_alive_mask left ON THE DEVICE: *mask_dev = device address of nsp bytes (valid on the model's stream
+ * after the launch), so the logical-or all-reduce of SpatialModel::condense (MPI_LOR, :182-186) runs on it in place, without a
+ * host round trip before the collective; the reduced mask is then read once and handed to eco_condense_apply */
+int eco_alive_mask_device(eco_model* m, void** mask_dev, size_t nsp);
 /* device pointers + byte size of the two boundary rows to send and the two ghost rows to fill */
 int eco_halo_ptrs(eco_model* m, void** send_top, void** send_bottom, void** recv_top, void** recv_bottom,
                   size_t* row_bytes);

@@ -13,6 +13,7 @@ U32 = ("interaction.row", "interaction.col")
 
 class SlabRank:
     """The `ops` protocol of ecolab_b200.spatial over an oracle slab."""
+    _TAILS_F64, _TAILS_U32 = F64, U32     # the arrays ModelData::mutate appends to (dist_mutate broadcasts their tails)
 
     def __init__(self, O, p, dens, nx, ny, comm, seed):
         self.O, self.nx, self.ny, self.comm = O, nx, ny, comm
