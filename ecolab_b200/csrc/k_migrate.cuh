@@ -123,8 +123,14 @@ __device__ __forceinline__ void mig_finish(MigState& k, const int4 nv, int e, in
 // row again (difference 0 -> flux 0).  NB rows are in flight per warp in registers; a row's load is re-issued the
 // moment the row is unpacked.
 // =====================================================================================================================
-constexpr int kMigThreads = 256;
-constexpr int kMigRowsInFlight = 5;   // measured on C3 (ms): 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04 (round 1)
+#ifndef ECO_MIG_THREADS
+#define ECO_MIG_THREADS 256
+#endif
+#ifndef ECO_MIG_NB
+#define ECO_MIG_NB 6   // rows in flight per warp; C4 / C3 ms with the dynamic unit order: 4: 24.6 / -, 5: 23.5 / 1.567, 6: 23.0 / 1.551, 7: 25.4 / 1.531 (spills), 8: 26.2 / 1.715
+#endif
+constexpr int kMigThreads = ECO_MIG_THREADS;
+constexpr int kMigRowsInFlight = ECO_MIG_NB;   // (round 1, static unit order, C3: 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04)   // measured on C3 (ms): 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04 (round 1)
 
 template <bool DUALE, bool RAG, int NB>
 __device__ __forceinline__ void mig_unit(const int32_t* __restrict__ p0, const int32_t* __restrict__ pn,
@@ -192,7 +198,7 @@ __device__ __forceinline__ void mig_wait_flag(const unsigned int* flag, unsigned
 }
 
 template <int TW>
-__global__ void __launch_bounds__(kMigThreads, 2) migrate_kernel(const MigParams p) {
+__global__ void __launch_bounds__(kMigThreads, 512 / kMigThreads) migrate_kernel(const MigParams p) {
   constexpr int QPR = TW / 4, RW = 32 / QPR;   // lanes per species row, species rows per warp
   constexpr bool DUALE = QPR == 1;
   const Layout& L = p.L;

@@ -19,7 +19,7 @@ if [ "$1" = build ]; then
   ls -la tools/variants
 else
   shift
-  B="python bench.py --steps 10 --warmup 3 --nx 1024 --ny 1024 --no-cpu --no-e2e --no-extra --no-verify $*"
+  B="python bench.py --steps 10 --warmup 3 ${VARGRID:---nx 1024 --ny 1024} --no-cpu --no-e2e --no-extra --no-verify $*"
   : > gpurun_out/variants.log
   for lib in default tools/variants/lib_*.so; do
     if [ $lib = default ]; then unset ECOLAB_B200_LIB; else export ECOLAB_B200_LIB=$PWD/$lib; fi
