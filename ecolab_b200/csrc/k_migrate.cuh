@@ -130,7 +130,7 @@ __device__ __forceinline__ void mig_finish(MigState& k, const int4 nv, int e, in
 #define ECO_MIG_NB 6   // rows in flight per warp; C4 / C3 ms with the dynamic unit order: 4: 24.6 / -, 5: 23.5 / 1.567, 6: 23.0 / 1.551, 7: 25.4 / 1.531 (spills), 8: 26.2 / 1.715
 #endif
 constexpr int kMigThreads = ECO_MIG_THREADS;
-constexpr int kMigRowsInFlight = ECO_MIG_NB;   // (round 1, static unit order, C3: 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04)   // measured on C3 (ms): 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04 (round 1)
+constexpr int kMigRowsInFlight = ECO_MIG_NB;   // (round 1, static unit order, C3: 2: 1.67  3: 1.73  4: 1.63  5: 1.60  6: 1.89  8: 2.04)
 
 template <bool DUALE, bool RAG, int NB>
 __device__ __forceinline__ void mig_unit(const int32_t* __restrict__ p0, const int32_t* __restrict__ pn,
