@@ -255,10 +255,10 @@ def run_native(args):
     traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        # the capture of a launch of this very grid where there is one (C4, C3); a slab of the C4 grid (N > 1) uses the
-        # capture of the whole-grid launch -- same kernel, same rows, fewer of them
+        # the capture of a launch of this grid width whose row count is closest to this rank's (C4 whole, a 512-row slab of it, C3)
         cand = [e for e in json.load(open(tp)).get("entries", []) if e["kernel"] == name and e["nnz"] == args.nnz and e["nsp"] == args.nsp]
-        exact = [e for e in cand if e["grid"] == [nx, ny]] or [e for e in cand if e["grid"][0] == nx]
+        rows = m._y1 - m._y0
+        exact = sorted((e for e in cand if e["grid"][0] == nx), key=lambda e: abs(e["grid"][1] - rows))
         if exact:
             traffic = exact[0]["dram_bytes_per_update"] * local_updates
             traffic_src = exact[0]["source"]
