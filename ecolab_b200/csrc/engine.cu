@@ -174,6 +174,7 @@ void Engine::resize_species(uint32_t nsp) {
   CK(cudaSetDevice(device_));
   if (nsp <= cap_) {
     if (nsp > nsp_ && buf_[cur_]) {   // re-zero the rows being brought to life (ghost rows too)
+      bounds_sync();
       const uint32_t ntiles_all = ntx_ * (ny_ + 2);
       zero_rows_kernel<<<(unsigned)std::min<unsigned long long>(4096, (unsigned long long)ntiles_all * (nsp - nsp_) * tw_ / 256 + 1),
                          256, 0, ST>>>(LAYOUT(cur_), ntiles_all, buf_[cur_], nsp_, nsp);
@@ -200,6 +201,9 @@ void Engine::resize_species(uint32_t nsp) {
   int32_t* nb = nullptr;
   CK(cudaMalloc(&nb, bytes));
   CK(cudaMemsetAsync(nb, 0, bytes, ST));
+  buf_[0] = nb;
+  cur_ = 0;
+  bounds_sync(old_cur, (size_t)(ny_ + 2) * S.row_stride * sizeof(int32_t));   // the new buffer + the one being read
   if (old_cur && old_nsp) {
     const Layout D = make_layout(nb, tw_, cap_, ntx_, nx_, ny_ + 2, y0_, nyg_, nsp);
     const unsigned long long n = (unsigned long long)(ny_ + 2) * old_nsp * std::min(S.ntx * S.tw, D.ntx * D.tw);
@@ -241,6 +245,7 @@ void Engine::get_density(size_t cell, int32_t* d, size_t n) {
 
 void Engine::set_density_all_dev(const int32_t* dev, size_t nsp) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   if (nsp != nsp_) throw std::runtime_error("set_density_all: species count mismatch");
   const unsigned long long nwork = (unsigned long long)((nx_ + 31) / 32) * ny_ * ((nsp_ + 31) / 32);
   if (!nwork) return;
@@ -252,6 +257,7 @@ void Engine::set_density_all_dev(const int32_t* dev, size_t nsp) {
 
 void Engine::get_density_all_dev(int32_t* dev, size_t nsp) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   if (nsp != nsp_) throw std::runtime_error("get_density_all: species count mismatch");
   const unsigned long long nwork = (unsigned long long)((nx_ + 31) / 32) * ny_ * ((nsp_ + 31) / 32);
   if (!nwork) return;
@@ -288,6 +294,7 @@ void Engine::get_density_all(int32_t* host, size_t nsp) {
 
 void Engine::get_density_rows(uint32_t r0, uint32_t nrows, int32_t* host, size_t nsp) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   if (nsp != nsp_) throw std::runtime_error("get_density_rows: species count mismatch");
   if ((uint64_t)r0 + nrows > ny_) throw std::runtime_error("get_density_rows: rows outside the owned slab");
   const size_t n = (size_t)nx_ * nrows * nsp;
@@ -308,6 +315,7 @@ void Engine::get_density_rows(uint32_t r0, uint32_t nrows, int32_t* host, size_t
 
 void Engine::set_density_rows(uint32_t r0, uint32_t nrows, const int32_t* host, size_t nsp) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   if (nsp != nsp_) throw std::runtime_error("set_density_rows: species count mismatch");
   if ((uint64_t)r0 + nrows > ny_) throw std::runtime_error("set_density_rows: rows outside the owned slab");
   const size_t n = (size_t)nx_ * nrows * nsp;
@@ -328,6 +336,7 @@ void Engine::set_density_rows(uint32_t r0, uint32_t nrows, const int32_t* host, 
 
 void Engine::fill_density(int32_t v) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   const uint32_t ntiles = ntx_ * ny_;
   if (!ntiles || !nsp_) return;
   fill_kernel<<<(unsigned)std::min<unsigned long long>(148 * 32, (unsigned long long)ntiles * nsp_ * tw_ / 256 + 1), 256, 0, ST>>>(
@@ -338,6 +347,7 @@ void Engine::fill_density(int32_t v) {
 
 void Engine::fill_density_random(uint32_t seed, int32_t lo, int32_t hi) {
   CK(cudaSetDevice(device_));
+  bounds_sync();
   const uint32_t ntiles = ntx_ * ny_;
   if (!ntiles || !nsp_) return;
   const unsigned long long n = (unsigned long long)ntiles * nsp_ * (tw_ / 4);

@@ -135,6 +135,10 @@ class Engine {
   void last_kernel_config(int* grid, int* block, int* smem) const {
     *grid = last_grid_; *block = last_block_; *smem = last_smem_;
   }
+  // bounds-assert build (-DECO_BOUNDS): registers the ranges the kernels may touch / reads the violation count; no-ops otherwise
+  void bounds_sync(const void* extra = nullptr, size_t extra_bytes = 0);
+  unsigned bounds_bad(unsigned* site = nullptr, unsigned long long* addr = nullptr);
+  unsigned bounds_selftest();
   // tuning knobs (bench/profiling): 0 = auto.  gen_stages: shared-memory tile buffers of the generate pipeline
   int gen_stages = 0;
   int gen_nobsmem = 0;   // 1: never stage beta in shared memory

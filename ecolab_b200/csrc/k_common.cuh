@@ -90,6 +90,41 @@ __device__ __forceinline__ int round_stoch_inrange(double x, uint32_t u) {
   return __double2loint(t) + (cp > u ? 1 : 0);
 }
 
+// ---- bounds-assert build (-DECO_BOUNDS; libecolab_b200_bounds.so, tests/test_gpu_bounds.py) ---------------------------
+// compute-sanitizer cannot run on the GPU pool, so the same question -- does any kernel touch a byte outside the density
+// buffers? -- is answered by a second build of the library in which every global access of the kernels that move densities
+// is checked against the table of registered ranges (this rank's two buffers, the old buffer during a re-layout, the
+// neighbour ranks' boundary rows).  A violation records its site and address; nothing is checked in the product build.
+#ifdef ECO_BOUNDS
+struct BoundsTable {
+  const char* lo[6];
+  const char* hi[6];
+  unsigned int bad;            // number of violations
+  unsigned int site;           // site code of the last one
+  unsigned long long addr;     // its address
+};
+__device__ BoundsTable g_eco_bounds;
+__device__ __forceinline__ void eco_chk(const void* ptr, size_t bytes, unsigned int site) {
+  const char* c = static_cast<const char*>(ptr);
+  bool ok = false;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) ok |= g_eco_bounds.lo[i] != nullptr && c >= g_eco_bounds.lo[i] && c + bytes <= g_eco_bounds.hi[i];
+  if (!ok) {
+    atomicAdd(&g_eco_bounds.bad, 1u);
+    g_eco_bounds.site = site;
+    g_eco_bounds.addr = (unsigned long long)ptr;
+  }
+}
+#define ECO_CHK(ptr, bytes, site) ::eco::eco_chk((ptr), (bytes), (site))
+// negative control for the test: one access that is in range and one that straddles the end of the buffer
+__global__ void bounds_selftest_kernel(const int32_t* buf, size_t ints) {
+  ECO_CHK(buf + ints - 4, 16, 90u);   // the last 16 bytes: fine
+  ECO_CHK(buf + ints - 3, 16, 91u);   // 4 bytes past the end: must be reported
+}
+#else
+#define ECO_CHK(ptr, bytes, site) ((void)0)
+#endif
+
 // ---- mbarrier / bulk-copy (TMA unit) wrappers ------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

@@ -273,6 +273,7 @@ __device__ __forceinline__ void round4x2(const double (&x)[2][4], const uint4 u0
 }
 
 __device__ __forceinline__ void load_tile_bulk(int32_t* dst_smem, const int32_t* src, uint32_t tile_bytes, uint64_t* bar) {
+  ECO_CHK(src, tile_bytes, 10u);
   mbar_expect_tx(bar, tile_bytes);
   for (uint32_t off = 0; off < tile_bytes; off += 32768u) {   // modest requests, one barrier
     const uint32_t n = min(32768u, tile_bytes - off);
@@ -366,6 +367,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
         const uint4 u0 = philox_rk(xq, yg, row0, (uint32_t)p.t0, p.rk), u1 = philox_rk(xq, yg, row0 + R, (uint32_t)p.t0, p.rk);
         int4 o0, o1;
         round4x2(x, u0, u1, o0, o1);
+        ECO_CHK(gl + b0 * (R * TW), 16, 11u);
+        ECO_CHK(gl + (b0 + 1) * (R * TW), 16, 11u);
         __stcs(reinterpret_cast<int4*>(gl + b0 * (R * TW)), o0);
         __stcs(reinterpret_cast<int4*>(gl + (b0 + 1) * (R * TW)), o1);
       }
@@ -378,6 +381,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
           double x[4];
           gen_x<TW, BSMEM, -1, true, FMA>(lp, own, blk, W, x);
           const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
+          ECO_CHK(gl + b * (R * TW), 16, 12u);
           __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
         }
       }
@@ -420,6 +424,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) generate_pipe_kernel(const G
       double x[4];
       gen_x<TW, BSMEM, -1, true, FMA>(lp, own, blk, W, x);
       const int4 o = round4(x, philox_rk(xq, yg, row, (uint32_t)p.t0, p.rk));
+      ECO_CHK(gl + b * (R * TW), 16, 13u);
       __stcs(reinterpret_cast<int4*>(gl + b * (R * TW)), o);
     }
     first += NW - nbm;
@@ -500,6 +505,7 @@ __global__ void __launch_bounds__(THREADS, 1) generate_multi_kernel(const GenPar
     }
     const int4* s4 = reinterpret_cast<const int4*>(src);
     int4* g4 = reinterpret_cast<int4*>(gt);
+    ECO_CHK(gt, tile_bytes, 14u);
     for (uint32_t i = threadIdx.x; i < tile_words / 4; i += THREADS) g4[i] = s4[i];
     __syncthreads();   // everyone done reading the buffers before the next bulk copy lands
   }

@@ -55,10 +55,12 @@ struct MigRow {
 template <bool DUALE>
 __device__ __forceinline__ MigRow mig_load(const int32_t* p, long long eoff, long long eoff2) {
   MigRow m;
+  ECO_CHK(p, 16, 20u);
+  ECO_CHK(p + eoff, 4, 21u);
   m.v = *reinterpret_cast<const int4*>(p);
   m.e = *(p + eoff);
   m.e2 = 0;
-  if (DUALE) m.e2 = *(p + eoff2);
+  if (DUALE) { ECO_CHK(p + eoff2, 4, 22u); m.e2 = *(p + eoff2); }
   return m;
 }
 
@@ -110,6 +112,7 @@ __device__ __forceinline__ void mig_finish(MigState& k, const int4 nv, int e, in
   const int d0 = k.tn.x - ts.x + hs.x, d1 = k.tn.y - ts.y + hs.y, d2 = k.tn.z - ts.z + hs.z, d3 = k.tn.w - ts.w + hs.w;
   const int4 out = make_int4(__double2loint(k.b[0]) + d0, __double2loint(k.b[1]) + d1, __double2loint(k.b[2]) + d2,
                              __double2loint(k.b[3]) + d3);
+  ECO_CHK(dp, 16, 23u);
   __stcs(reinterpret_cast<int4*>(dp), out);   // streaming (evict-first): the row is not read again by this kernel
   acc += (unsigned long long)((uint32_t)abs(d0) + (uint32_t)abs(d1)) + (unsigned long long)((uint32_t)abs(d2) + (uint32_t)abs(d3));
   k.b[0] = nb[0]; k.b[1] = nb[1]; k.b[2] = nb[2]; k.b[3] = nb[3];
@@ -138,6 +141,7 @@ __device__ __forceinline__ void mig_unit(const int32_t* __restrict__ p0, const i
                                          long long eoff, long long eoff2, double c, bool first_q, bool last_q, uint32_t rag,
                                          unsigned long long& acc) {
   auto rowp = [&](uint32_t r) -> const int32_t* { return r < n ? p0 + (long long)r * stride : ps; };
+  ECO_CHK(pn, 16, 24u);
   const int4 up = *reinterpret_cast<const int4*>(pn);
   const MigRow first = mig_load<DUALE>(p0, eoff, eoff2);
   MigRow r[NB];                                                                             // rows i+1 .. i+NB, in flight

@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(256) compact_kernel(int32_t* buf, size_t tile_
         const uint32_t sp = s0 + u * rows + rr;
         dst[u] = 0xffffffffu;
         if (sp < nsp_old) {
+          ECO_CHK(t + (size_t)sp * tw, 16, 30u);
           v[u] = *reinterpret_cast<const int4*>(t + (size_t)sp * tw);
           if (__ldg(keep + sp)) dst[u] = __ldg(map + sp);
         }
@@ -63,10 +64,10 @@ __global__ void __launch_bounds__(256) compact_kernel(int32_t* buf, size_t tile_
       __syncwarp();
 #pragma unroll
       for (int u = 0; u < U; ++u)
-        if (dst[u] != 0xffffffffu) *reinterpret_cast<int4*>(t + (size_t)dst[u] * tw) = v[u];
+        if (dst[u] != 0xffffffffu) { ECO_CHK(t + (size_t)dst[u] * tw, 16, 31u); *reinterpret_cast<int4*>(t + (size_t)dst[u] * tw) = v[u]; }
       __syncwarp();
     }
-    for (uint32_t sp = nkeep + rr; sp < nsp_old; sp += rows) *reinterpret_cast<int4*>(t + (size_t)sp * tw) = make_int4(0, 0, 0, 0);
+    for (uint32_t sp = nkeep + rr; sp < nsp_old; sp += rows) { ECO_CHK(t + (size_t)sp * tw, 16, 32u); *reinterpret_cast<int4*>(t + (size_t)sp * tw) = make_int4(0, 0, 0, 0); }
   }
 }
 
@@ -213,6 +214,7 @@ __global__ void __launch_bounds__(256) mutate_emit_kernel(const Layout L, const 
       int born[4] = {0, 0, 0, 0};
       int4 v = make_int4(0, 0, 0, 0);
       if (i < per) {
+        ECO_CHK(tp + i, 16, 41u);
         v = tp[i];
         mutate_born(L, v, __ldg(ms + s), tx * qpr + qd, yg, s, t, seed, born);
       }
@@ -234,9 +236,11 @@ __global__ void __launch_bounds__(256) mutate_emit_kernel(const Layout L, const 
           if (born[k] > 0) {
             uint32_t pos = base[4 * qd + k] + rank[k];
             for (uint32_t w = 0; w < warp; ++w) pos += wcnt[w][4 * qd + k];
+            ECO_CHK(rec + pos, sizeof(MutRec), 43u);
             rec[pos] = MutRec{yg * L.nx + tx * L.tw + 4 * qd + k, s, (uint32_t)born[k]};
             n[k] -= born[k];
           }
+        ECO_CHK(tp + i, 16, 42u);
         tp[i] = make_int4(n[0], n[1], n[2], n[3]);
       }
       __syncthreads();
@@ -257,6 +261,7 @@ __global__ void zero_rows_kernel(const Layout L, uint32_t ntiles_all, int32_t* b
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (unsigned long long)gridDim.x * blockDim.x) {
     const uint32_t tile = (uint32_t)(i / per_tile), o = (uint32_t)(i % per_tile);
+    ECO_CHK(&buf[(size_t)tile * L.tile_stride + (size_t)s0 * L.tw + o], 4, 40u);
     buf[(size_t)tile * L.tile_stride + (size_t)s0 * L.tw + o] = 0;
   }
 }
@@ -266,6 +271,7 @@ __global__ void birth_kernel(const Layout L, uint32_t s0, const uint32_t* cells,
   const uint32_t c = cells[i];
   const uint32_t yg = c / L.nx, x = c - yg * L.nx;
   if (yg < L.y0 || yg >= L.y0 + L.ny) return;
+  ECO_CHK(&L.base[cell_addr(L, yg - L.y0, x, s0 + i)], 4, 33u);
   L.base[cell_addr(L, yg - L.y0, x, s0 + i)] = 1;
 }
 
@@ -326,10 +332,11 @@ __global__ void __launch_bounds__(1024) transpose_kernel(const Layout L, int32_t
       sm[ty_][tx_] = (x < L.nx && s < L.nsp) ? cellmajor[((size_t)yl * L.nx + x) * L.nsp + s] : 0;
       __syncthreads();
       const uint32_t s2 = sb * 32u + ty_, x2 = xb * 32u + tx_;   // write coalesced along cells
-      if (s2 < L.nsp && x2 < L.ntx * L.tw) L.base[cell_addr(L, yl, x2, s2)] = (x2 < L.nx) ? sm[tx_][ty_] : 0;
+      if (s2 < L.nsp && x2 < L.ntx * L.tw) { ECO_CHK(&L.base[cell_addr(L, yl, x2, s2)], 4, 34u); L.base[cell_addr(L, yl, x2, s2)] = (x2 < L.nx) ? sm[tx_][ty_] : 0; }
       __syncthreads();
     } else {
       const uint32_t s2 = sb * 32u + ty_, x2 = xb * 32u + tx_;
+      if (s2 < L.nsp && x2 < L.nx) ECO_CHK(&L.base[cell_addr(L, yl, x2, s2)], 4, 35u);
       sm[ty_][tx_] = (s2 < L.nsp && x2 < L.nx) ? L.base[cell_addr(L, yl, x2, s2)] : 0;
       __syncthreads();
       const uint32_t x = xb * 32u + ty_, s = sb * 32u + tx_;
@@ -348,6 +355,8 @@ __global__ void relayout_kernel(const Layout S, const Layout D, uint32_t nrows_y
        i += (unsigned long long)gridDim.x * blockDim.x) {
     const uint32_t x = (uint32_t)(i % xw);
     const uint32_t s = (uint32_t)((i / xw) % nrows_s), y = (uint32_t)(i / ((unsigned long long)xw * nrows_s));
+    ECO_CHK(&D.base[cell_addr(D, y, x, s)], 4, 36u);
+    ECO_CHK(&S.base[cell_addr(S, y, x, s)], 4, 37u);
     D.base[cell_addr(D, y, x, s)] = S.base[cell_addr(S, y, x, s)];
   }
 }
@@ -359,6 +368,7 @@ __global__ void fill_kernel(const Layout L, int32_t v) {
        i += (unsigned long long)gridDim.x * blockDim.x) {
     const uint32_t tile = (uint32_t)(i / per_tile), o = (uint32_t)(i % per_tile);
     const uint32_t tx = tile % L.ntx;
+    ECO_CHK(&L.base[(size_t)tile * L.tile_stride + o], 4, 38u);
     L.base[(size_t)tile * L.tile_stride + o] = (tx * L.tw + o % L.tw < L.nx) ? v : 0;
   }
 }
@@ -378,6 +388,7 @@ __global__ void __launch_bounds__(256) fill_random_kernel(const Layout L, uint32
     v.y = xq * 4 + 1 < L.nx ? lo + (int32_t)(u.y % span) : 0;
     v.z = xq * 4 + 2 < L.nx ? lo + (int32_t)(u.z % span) : 0;
     v.w = xq * 4 + 3 < L.nx ? lo + (int32_t)(u.w % span) : 0;
+    ECO_CHK(reinterpret_cast<int4*>(L.base + (size_t)tile * L.tile_stride) + i, 16, 39u);
     reinterpret_cast<int4*>(L.base + (size_t)tile * L.tile_stride)[i] = v;
   }
 }

@@ -676,6 +676,9 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "numY") *out = (double)m->numY;
   else if (s == "maxNbrs") *out = (double)m->maxNbrs;
   else if (s == "launches") *out = (double)m->eng.launches();
+  else if (s == "bounds_bad") *out = (double)m->eng.bounds_bad();                      // bounds-assert build only (0 otherwise)
+  else if (s == "bounds_selftest") *out = (double)m->eng.bounds_selftest();
+  else if (s == "bounds_site") { unsigned st = 0; m->eng.bounds_bad(&st); *out = (double)st; }
   else if (s == "last_block") { int g, b, sm; m->eng.last_kernel_config(&g, &b, &sm); *out = (double)b; }   // threads per CTA of the last hot kernel
   else if (s == "last_smem") { int g, b, sm; m->eng.last_kernel_config(&g, &b, &sm); *out = (double)sm; }
   else if (s == "device_bytes") *out = (double)m->eng.bytes_allocated();
