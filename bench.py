@@ -359,6 +359,22 @@ def extra_legs(E, args, local, stream):
                            "generate_hbm_frac": 8.0 * 2 ** 30 / (g * 1e-3) / 1e9 / peaks()[0]}
         m.close(); del m
     out["nnz_sweep_c3"] = {"workload": "spatial 1024x1024 cells x 1024 species, generate(1)+migrate(), 5 steps", "by_nnz_per_row": sweep}
+    # the scripts' step on a big grid: generate(100) then ONE migrate (models/steady_migration.py:63-71) -- the 100 sub-steps of a
+    # tile run on chip (generate_multi_kernel), so HBM sees 8/100 B per update-step
+    a = copy.copy(args); a.nnz = 3
+    m = build_model(E, a, 1024, 1024, None, local, stream)
+    m.step(100, wait=False)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(2):
+        m.step(100, wait=False)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms100 = e0.elapsed_time(e1) / 2
+    out["generate100_migrate_c3"] = {"workload": "spatial 1024x1024 cells x 1024 species, 3 nnz/row: generate(100)+migrate() per round, 2 rounds",
+                                     "ms_per_round": ms100, "update_steps_per_s": 2 ** 30 * 100 / (ms100 * 1e-3)}
+    m.close(); del m
     # the scripts' cadence (models/spatial_ecolab.py:66-78) at BASELINE.json config 2's shape
     a = copy.copy(args); a.nsp = 1000; a.nnz = 3
     rounds = 4
