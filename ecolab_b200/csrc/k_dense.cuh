@@ -7,7 +7,8 @@
 // a density is  n = sum_q b_q 256^q,  b_q in [0,255]  (B operand, u8).  Every slice product a_p x b_q is an
 // s8 x u8 -> s32 GEMM whose K-sum is EXACT (8192 x 128 x 255 < 2^31 leaves room for 8 products per accumulator);
 // products of equal weight 256^g, g = q-p+P-1, share one TMEM accumulator ("group").  The epilogue recombines
-//     S = 2^-s_i * sum_g 256^g acc_g            (Horner in FP64: exact while the integer stays below 2^53)
+//     S = 2^-s_i * sum_g 256^g acc_g            (Horner in FP64: exact while the integer stays below 2^53, i.e. while
+//                                                nsp * 2^(8P-1) * max n < 2^53; beyond that it rounds to 2^-53 relative)
 //     ir = diag*n + S ;  x = n + n*(r + ir) ;  n' = ROUND(x)   with the same Philox draw as the sparse kernel.
 // The only approximation is the rounding of beta to 8P-1 bits relative to its row maximum (P = 3: 2^-24, P = 7:
 // beyond FP64), so the pre-rounding x agrees with the FP64 sequential sum to ~1e-9 (P = 3) and the integer results
@@ -367,7 +368,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
           double sum[4];
 #pragma unroll
           for (uint32_t e = 0; e < 4; ++e) {
-            // Horner over the weight groups.  fma is used ONLY here, on integers below 2^53: t*256 + acc is exact, so the
+            // Horner over the weight groups.  fma is used ONLY here; on integers below 2^53 t*256 + acc is exact, so the
             // fused and the two-step form give the same bits (the reference-order arithmetic below stays unfused).
             double t = 0.0;
             bool started = false;
