@@ -31,7 +31,9 @@ CASES = [
     ("steady_migration.py", 25),              # generate(100)+mutate+migrate+condense, writes steady.dat
     ("fragmentation_pump.py", 25),            # the same with the migration pump, writes pump.dat
     ("SAR.py", 12),                           # first ensemble member (1 x 1 grid, 30 species)
+    ("SAR1.py", 12),                          # the variant that takes the migration rate from its command line
 ]
+ARGS = {"SAR1.py": ["1e-3"]}
 
 
 @pytest.mark.parametrize("script,budget", CASES)
@@ -39,7 +41,7 @@ def test_reference_script_unchanged_against_oracle(oracle_mod, gpu, tmp_path, mo
     import shadow
     monkeypatch.chdir(tmp_path)
     monkeypatch.setenv("ECOLAB_STEPS", "6")
-    monkeypatch.setattr(sys, "argv", [script])
+    monkeypatch.setattr(sys, "argv", [script] + ARGS.get(script, []))
     mod = shadow.install(oracle_mod, budget)
     try:
         try:

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.skipif(not os.path.isdir(REF), reason="reference checko
 
 
 def test_model_scripts_are_verbatim():
-    for f in ("spatial_ecolab", "steady_migration", "fragmentation_pump", "SAR", "panmictic_ecolab", "pred-prey", "migration_test"):
+    for f in ("spatial_ecolab", "steady_migration", "fragmentation_pump", "SAR", "SAR1", "panmictic_ecolab", "pred-prey", "migration_test"):
         assert open(os.path.join(HERE, f + ".py"), "rb").read() == open(os.path.join(REF, "models", f + ".py"), "rb").read(), f
 
 
