@@ -295,3 +295,25 @@ def test_spatial_ecolab_sh(mods):
             for k in range(nsp):
                 n1[k] += d[k]
     assert n0 == n1 and moved >= 0
+
+
+def test_checkpoint_restart_sh(gpu, tmp_path):
+    """test/checkpoint-restart.sh:38-76 (a TCL script in the reference; the same statements through the Python surface):
+    set the panmictic model, checkpoint, wipe two members, restart, every member is back."""
+    ecolab = gpu.PanmicticModel(0)      # a fresh model, as the freshly started `models/ecolab` interpreter of the script has
+    density, repro_rate, diag = [100, 100], [.1, -.1], [-.0001, 0]
+    val, row, col = [-0.001, 0.001], [0, 1], [1, 0]
+    ecolab.density(density)
+    ecolab.repro_rate(repro_rate)
+    ecolab.interaction.diag(diag)
+    ecolab.interaction.val(val)
+    ecolab.interaction.row(row)
+    ecolab.interaction.col(col)
+    f = str(tmp_path / "test.ckpt")
+    ecolab.checkpoint(f)
+    ecolab.repro_rate([])
+    ecolab.interaction.val([])
+    ecolab.restart(f)
+    assert ecolab.density() == density and ecolab.repro_rate() == repro_rate
+    assert ecolab.interaction.diag() == diag and ecolab.interaction.val() == val
+    assert ecolab.interaction.row() == row and ecolab.interaction.col() == col
