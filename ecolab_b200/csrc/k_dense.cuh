@@ -159,6 +159,29 @@ __device__ __forceinline__ void dense_issue_stage(uint32_t tmem, uint32_t a_lo, 
   }
 }
 
+// The same for ONE ROUND of a slicing with more than four weight groups (P + Q - 1 > 4: densities of 2^16 and more with three
+// beta slices): only the slice pairs whose group lies in [G0, G1) are issued, into accumulators numbered from G0.  Everything
+// is still a compile-time constant, so the issuing thread runs at the tensor pipe's pace instead of the ~300 cycles per MMA
+// of run-time slice loops (a Q = 3 step took 87 ms through those).
+template <int P, int Q, int G0, int G1, bool FIRST>
+__device__ __forceinline__ void dense_issue_stage_range(uint32_t tmem, uint32_t a_lo, uint32_t b_lo) {
+#pragma unroll
+  for (int ks = 0; ks < (int)(DENSE_KC / 32); ++ks) {
+#pragma unroll
+    for (int pp = 0; pp < P; ++pp) {
+      const uint64_t ad = umma_desc(a_lo + pp * (DENSE_TILE_BYTES >> 4) + ks * 2);
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int g = q + P - 1 - pp;
+        if (g < G0 || g >= G1) continue;
+        // group g was touched before, in this K step, by (pp-1, q-1) when both exist (same g, earlier in the loop order)
+        umma_i8(tmem + (g - G0) * 128, ad, umma_desc(b_lo + q * (DENSE_TILE_BYTES >> 4) + ks * 2), DENSE_IDESC128,
+                (FIRST && ks == 0 && !(pp > 0 && q > 0)) ? 0u : 1u);
+      }
+    }
+  }
+}
+
 // ---- B operand: int32 densities -> Q u8 slices in the shared-memory image layout ---------------------------------------
 // One thread = 16 consecutive species x one cell quad: 16 LDG.128 (contiguous 256 B when TW = 4) -> 4*Q STG.128.
 __global__ void __launch_bounds__(256) dense_pack_kernel(const Layout L, uint8_t* __restrict__ bop, uint32_t Q, uint32_t nkc,
@@ -260,8 +283,9 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     // ===================== MMA issuer =====================
     if (lane == 0) {
       long long pc[3] = {0, 0, 0};
-      // single-round launches of the common slicings take the compile-time issue path
-      const uint32_t fast = (p.g0 == 0 && p.g1 == P + Q - 1u) ? P * 10u + Q : 0u;
+      // compile-time issue paths: single-round launches of the common slicings, and the two rounds of P = 3 with Q = 3 / 4
+      const uint32_t fast = (p.g0 == 0 && p.g1 == P + Q - 1u) ? P * 10u + Q
+                            : (P == 3u && (Q == 3u || Q == 4u) && (p.g0 == 0u || p.g0 == 4u)) ? 1000u + Q * 10u + p.g0 : 0u;
       uint32_t stage = 0, round = 0, k = 0;
       for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
         uint32_t mt, nt;
@@ -284,6 +308,10 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
           else if (fast == 21u) { if (kc) dense_issue_stage<2, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<2, 1, true>(tmem, a_lo, b_lo); }
           else if (fast == 22u) { if (kc) dense_issue_stage<2, 2, false>(tmem, a_lo, b_lo); else dense_issue_stage<2, 2, true>(tmem, a_lo, b_lo); }
           else if (fast == 41u) { if (kc) dense_issue_stage<4, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<4, 1, true>(tmem, a_lo, b_lo); }
+          else if (fast == 1030u) { if (kc) dense_issue_stage_range<3, 3, 0, 4, false>(tmem, a_lo, b_lo); else dense_issue_stage_range<3, 3, 0, 4, true>(tmem, a_lo, b_lo); }
+          else if (fast == 1034u) { if (kc) dense_issue_stage_range<3, 3, 4, 5, false>(tmem, a_lo, b_lo); else dense_issue_stage_range<3, 3, 4, 5, true>(tmem, a_lo, b_lo); }
+          else if (fast == 1040u) { if (kc) dense_issue_stage_range<3, 4, 0, 4, false>(tmem, a_lo, b_lo); else dense_issue_stage_range<3, 4, 0, 4, true>(tmem, a_lo, b_lo); }
+          else if (fast == 1044u) { if (kc) dense_issue_stage_range<3, 4, 4, 6, false>(tmem, a_lo, b_lo); else dense_issue_stage_range<3, 4, 4, 6, true>(tmem, a_lo, b_lo); }
           else {
             // any other slicing / a multi-round launch: run-time loops (correct, slower to issue)
 #pragma unroll
