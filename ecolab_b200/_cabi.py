@@ -70,6 +70,7 @@ SIGNATURES = {
     "eco_mutant_connectivity": [_vp, _sz, _P(_dbl)],
     "eco_extinction_connectivity": [_vp, _P(_dbl)],
     "eco_species_totals": [_vp, _vp, _sz],
+    "eco_species_totals_noalloc": [_vp, _vp, _sz],
     "eco_checkpoint": [_vp, _cp],
     "eco_restart": [_vp, _cp],
     "eco_migrate_local": [_vp, _P(_u64)],

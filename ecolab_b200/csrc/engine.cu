@@ -11,7 +11,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
+#include <string>
 
 #include "k_common.cuh"
 #include "k_generate.cuh"
@@ -34,6 +36,8 @@ void check_cuda(int err, const char* what, const char* file, int line) {
 }
 
 namespace {
+
+unsigned long long* noalloc_totals_ptr(int device);   // engine_ops.inc: address of the static totals scratch on `device`
 
 constexpr size_t kSmemPerSm = 227 * 1024;
 inline uint32_t round_up32(uint32_t n) { return (n + 31u) & ~31u; }
@@ -79,6 +83,7 @@ Engine::Engine(int device) : device_(device) {
   cudaEvent_t ev;
   CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   ev_total_ = ev;
+  noalloc_totals_ptr(device_);   // set-up half of species_totals_noalloc(): resolve the static scratch once per device
 }
 
 Engine::~Engine() {

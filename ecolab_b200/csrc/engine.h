@@ -94,6 +94,10 @@ class Engine {
   void nsp_per_cell(uint32_t* out_host);
   // per-species totals over owned cells
   void species_totals(int64_t* out_host);
+  // the same with the accumulators in a static device array: no cudaMalloc / cudaFree, at most noalloc_max_species() species;
+  // `out` may be host or device memory.  Calls that overlap on one GPU race on the shared array.
+  void species_totals_noalloc(int64_t* out);
+  static uint32_t noalloc_max_species();
 
   // ---- multi-GPU halo -------------------------------------------------------
   // Device pointers of the boundary rows to send and the ghost rows to receive

@@ -982,6 +982,17 @@ int eco_species_totals(eco_model* m, int64_t* out, size_t nsp) {
   m->eng.species_totals(out);
   ECO_CATCH
 }
+int eco_species_totals_noalloc(eco_model* m, int64_t* out, size_t nsp) {
+  ECO_TRY
+  need(m);
+  if (nsp > eco::Engine::noalloc_max_species())
+    throw std::runtime_error("species_totals_noalloc: " + std::to_string(nsp) + " species exceed the static scratch of " +
+                             std::to_string(eco::Engine::noalloc_max_species()) + " (ECO_NOALLOC_MAX_SPECIES); use eco_species_totals");
+  if (nsp != m->eng.nsp()) throw std::runtime_error("species_totals_noalloc: species count differs from the model");
+  if (nsp && !out) throw std::runtime_error("species_totals_noalloc: null output");
+  m->eng.species_totals_noalloc(out);
+  ECO_CATCH
+}
 
 }  // extern "C"
 

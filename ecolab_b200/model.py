@@ -226,6 +226,16 @@ class EcolabModelBase:
             check(self._L.eco_species_totals(self._h, _ptr(a), ns))
         return a
 
+    def species_totals_noalloc(self, out=None):
+        """species_totals() through eco_species_totals_noalloc: static device scratch, no cudaMalloc on the call
+        (at most ECO_NOALLOC_MAX_SPECIES = 16384 species; no counterpart in the reference).  `out`: a caller-owned
+        int64 numpy array of nsp entries, allocated here when omitted."""
+        ns = int(self._scalar("nsp"))
+        a = np.empty(ns, dtype=np.int64) if out is None else out
+        if ns:
+            check(self._L.eco_species_totals_noalloc(self._h, _ptr(a), ns))
+        return a
+
     def pre_rounding(self):
         nc, ns = int(self._scalar("ncells_local")), int(self._scalar("nsp"))
         a = np.empty((nc, ns), dtype=np.float64)

@@ -144,6 +144,15 @@ int eco_mutant_connectivity(eco_model* m, size_t before_nsp, double* out);
 int eco_extinction_connectivity(eco_model* m, double* out);
 /* per-species totals over owned cells (conservation checks, reference :644,:662) */
 int eco_species_totals(eco_model* m, int64_t* out, size_t nsp);
+/* No counterpart in the reference: added for callers that may not reach cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as eco_species_totals, but the
+ * kernel's per-species accumulators live in a static device array of ECO_NOALLOC_MAX_SPECIES entries (128 KiB, held by
+ * every GPU that loads the library until exit): the call makes no cudaMalloc / cudaFree / allocating library call.
+ * nsp > ECO_NOALLOC_MAX_SPECIES is rejected (non-zero return, eco_last_error says so).  `out` (nsp int64) may be host or
+ * device memory.  All calls on one GPU share the array -- the used prefix is cleared before each launch -- so calls that
+ * overlap on the GPU (two models on one device driven concurrently) race; serialise them. */
+#define ECO_NOALLOC_MAX_SPECIES 16384
+int eco_species_totals_noalloc(eco_model* m, int64_t* out, size_t nsp);
 /* Model<M>::checkpoint / restart, include/ecolab.h:88-94 */
 int eco_checkpoint(eco_model* m, const char* file);
 int eco_restart(eco_model* m, const char* file);
