@@ -85,8 +85,10 @@ class ClockSampler:
         mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "sm_min_mhz": min(sm) if sm else None,
+                "power_w": float(np.median(pw)) if pw else None}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -566,7 +568,7 @@ def dense_leg(E, args, local, stream, steps, warmup, sparse_too=False):
         except Exception as ex:   # noqa: BLE001
             sparse_ms = f"unavailable: {ex}"
     if args.dense_prof:
-        names = ("mma_wait_tmem_empty", "mma_wait_smem_full", "mma_issue", "tiles", "epi_wait_tmem_full", "epi_work")
+        names = ("mma_wait_tmem_empty", "mma_wait_smem_full", "mma_issue", "tiles", "epi_wait_tmem_full", "epi_work", "epi_drain", "mma_loop_ns")
         roofline["cta0_cycles_last_launch"] = {n: int(m._scalar(f"dense_prof{i}")) for i, n in enumerate(names)}
     m.close(); del m
     return {"metric": METRIC, "value": updates * steps / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": steps,

@@ -59,6 +59,16 @@ uint32_t pick_tile_width(uint32_t cap) {
   throw std::runtime_error("species count exceeds the shared-memory tile (nsp*16 B must fit in 227 KB)");
 }
 
+// Capacity (species rows allocated) for nsp species: 25 % head-room so that speciation does not re-layout every round, but
+// never so much that the head-room alone costs a tile width -- the kernels stage nsp rows, the tile width is chosen for the
+// capacity (scripts' cadence at 64 x 64 cells: 3289 species under a 4288-row capacity ran generate(100) on 4-cell tiles).
+uint32_t pick_capacity(uint32_t nsp) {
+  const uint32_t cap = round_up32(nsp + nsp / 4 + 16);
+  for (uint32_t lim : {512u, 1760u, 3552u})   // largest capacities (multiples of 32) of the 32-, 16- and 8-cell tiles
+    if (nsp <= lim && cap > lim) return lim;
+  return cap;
+}
+
 }  // namespace
 
 // ===========================================================================================
@@ -190,7 +200,23 @@ void Engine::resize_species(uint32_t nsp) {
     return;
   }
   // grow: new capacity with head-room (and possibly a narrower tile), re-layout into a fresh buffer
-  const uint32_t new_cap = round_up32(nsp + nsp / 4 + 16);
+  relayout(pick_capacity(nsp), nsp);
+}
+
+// After species were removed: if the survivors fit a wider tile, re-layout to it (one pass over the densities, paid back by
+// the first generate()).  The decision depends on the species count and the GLOBAL grid only, so every rank of a
+// partitioned grid takes it alike (the halo rows are exchanged in layout order).
+void Engine::retile_after_shrink() {
+  if (!buf_[cur_] || !nsp_) return;
+  const uint32_t want_cap = pick_capacity(nsp_);
+  if (want_cap >= cap_ || pick_tile_width(want_cap) <= tw_) return;
+  if ((size_t)nx_ * nyg_ * want_cap * sizeof(int32_t) > ((size_t)16 << 30)) return;   // needs a second buffer: small grids only
+  CK(cudaSetDevice(device_));
+  relayout(want_cap, nsp_);
+}
+
+// move the densities into a fresh buffer of capacity new_cap (tile width chosen for it) holding nsp species
+void Engine::relayout(uint32_t new_cap, uint32_t nsp) {
   const uint32_t new_tw = pick_tile_width(new_cap);
   peer_disconnect();
   ++buf_version_;

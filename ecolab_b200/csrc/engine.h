@@ -105,6 +105,7 @@ class Engine {
   void halo_ptrs(void** send_top, void** send_bottom, void** recv_top, void** recv_bottom);
   size_t row_bytes() const { return (size_t)ntx_ * cap_ * tw_ * sizeof(int32_t); }
   uint32_t tile_width() const { return tw_; }
+  uint32_t capacity() const { return cap_; }
   // Halo over peer memory (CUDA IPC, NVLink): once connected, migrate's boundary units copy the neighbour slabs'
   // boundary rows straight out of the neighbours' buffers -- no ghost-row exchange, no collective.  Ordering is a
   // device-side epoch counter per rank: migrate() first publishes "everything before this migrate is done" (epoch e),
@@ -220,6 +221,8 @@ class Engine {
   int32_t* d_stage_ = nullptr; size_t stage_cap_ = 0;  // cell-major staging
   void* d_scratch_ = nullptr; size_t scratch_cap_ = 0;   // small per-call device temporaries (birth cells, species totals)
   void* scratch(size_t bytes);
+  void relayout(uint32_t new_cap, uint32_t nsp);   // densities into a fresh buffer of that capacity (tile width follows)
+  void retile_after_shrink();                      // condense: back to a wider tile when the survivors fit one
   int32_t* d_band_[4] = {nullptr, nullptr, nullptr, nullptr}; size_t band_cap_ = 0;   // step_host: 2 in + 2 out band stagings
   void* st_in_ = nullptr; void* st_out_ = nullptr;       // copy streams of step_host
   void* ev_band_[8] = {nullptr};

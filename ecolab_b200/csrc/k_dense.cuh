@@ -283,6 +283,8 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     // ===================== MMA issuer =====================
     if (lane == 0) {
       long long pc[3] = {0, 0, 0};
+      unsigned long long ns0 = 0;
+      if (p.prof) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns0));
       // compile-time issue paths: single-round launches of the common slicings, and the two rounds of P = 3 with Q = 3 / 4
       const uint32_t fast = (p.g0 == 0 && p.g1 == P + Q - 1u) ? P * 10u + Q
                             : (P == 3u && (Q == 3u || Q == 4u) && (p.g0 == 0u || p.g0 == 4u)) ? 1000u + Q * 10u + p.g0 : 0u;
@@ -332,7 +334,10 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
         umma_commit(&s_tfull);                            // accumulators complete
         ++k;
       }
-      if (p.prof) { p.prof[blockIdx.x * 8 + 0] = pc[0]; p.prof[blockIdx.x * 8 + 1] = pc[1]; p.prof[blockIdx.x * 8 + 2] = pc[2]; p.prof[blockIdx.x * 8 + 3] = k; }
+      if (p.prof) { p.prof[blockIdx.x * 8 + 0] = pc[0]; p.prof[blockIdx.x * 8 + 1] = pc[1]; p.prof[blockIdx.x * 8 + 2] = pc[2]; p.prof[blockIdx.x * 8 + 3] = k;
+        unsigned long long ns1;   // wall time of the issue loop: cycles / ns = the SM clock the kernel really ran at
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+        p.prof[blockIdx.x * 8 + 7] = ns1 - ns0; }
     }
   } else {
     // ===================== epilogue (warps 2..17; TMEM lanes 32*(warp%4).., columns DENSE_EPI_COLS*((warp-2)/4)..) =====================
@@ -341,7 +346,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     const uint32_t qsh = p.L.tw == 4 ? 0u : p.L.tw == 8 ? 1u : p.L.tw == 16 ? 2u : 3u;   // log2(quads per density tile)
     const double w0 = p.w0;
     const bool final_round = NGR ? true : !(p.flags & 2u), add_partial = NGR ? false : (p.flags & 1u) != 0;
-    long long ew = 0, ex = 0;
+    long long ew = 0, ed = 0, ex = 0;   // cycles: waiting for the accumulators, draining them, the update arithmetic
     uint32_t k = 0;
     // a cursor walks the padded quads of the slab in (row, x) order; null pointer = nothing to update there
     struct Cursor { uint32_t yl, xq; };
@@ -375,11 +380,44 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
       tc_fence_after();
       const long long e1 = clock64();
       ew += e1 - e0;
-#pragma unroll 2
-      for (uint32_t c0 = cbase; c0 < cbase + DENSE_EPI_COLS; c0 += DENSE_CHUNK) {
+      // Drain first: all of this warp's columns leave TMEM as recombined FP64 sums held in registers, the accumulators go
+      // back to the MMA warp at once, and the update arithmetic below overlaps the next tile's MMAs.
+      constexpr uint32_t NCH = DENSE_EPI_COLS / DENSE_CHUNK;
+      double hsum[NCH][DENSE_CHUNK];
+#pragma unroll
+      for (uint32_t ci = 0; ci < NCH; ++ci) {
+        int acc[DENSE_MAX_GROUPS][DENSE_CHUNK];
+#pragma unroll
+        for (uint32_t g = 0; g < DENSE_MAX_GROUPS; ++g)
+          if (g < ngr) tmem_ld8(tmem + ((lq * 32u) << 16) + g * 128u + cbase + ci * DENSE_CHUNK, acc[g]);
+#pragma unroll
+        for (uint32_t j = 0; j < DENSE_CHUNK; ++j) {
+          // Horner over the weight groups.  fma is used ONLY here; on integers below 2^53 t*256 + acc is exact, so the
+          // fused and the two-step form give the same bits (the reference-order arithmetic below stays unfused).
+          double t = 0.0;
+          bool started = false;
+#pragma unroll
+          for (int g = DENSE_MAX_GROUPS - 1; g >= 0; --g)
+            if ((uint32_t)g < ngr) {
+              t = started ? __fma_rn(t, 256.0, (double)acc[g][j]) : (double)acc[g][j];
+              started = true;
+            }
+          hsum[ci][j] = t;
+        }
+      }
+#ifndef ECO_DENSE_LATE_RELEASE
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_tempty);
+#endif
+      const long long e2 = clock64();
+      ed += e2 - e1;
+#pragma unroll
+      for (uint32_t ci = 0; ci < NCH; ++ci) {
+        const uint32_t c0 = cbase + ci * DENSE_CHUNK;
 #pragma unroll
         for (uint32_t qd = 0; qd < NQ; ++qd) own[qd] = nxt[qd];
-        if (c0 + DENSE_CHUNK < cbase + DENSE_EPI_COLS) {
+        if (ci + 1 < NCH) {
 #pragma unroll
           for (uint32_t qd = 0; qd < NQ; ++qd) {
             const int32_t* gp = quad_ptr(cp);
@@ -387,25 +425,12 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
             advance(cp);
           }
         }
-        int acc[DENSE_MAX_GROUPS][DENSE_CHUNK];
-#pragma unroll
-        for (uint32_t g = 0; g < DENSE_MAX_GROUPS; ++g)
-          if (g < ngr) tmem_ld8(tmem + ((lq * 32u) << 16) + g * 128u + c0, acc[g]);
 #pragma unroll
         for (uint32_t qd = 0; qd < NQ; ++qd) {
           double sum[4];
 #pragma unroll
           for (uint32_t e = 0; e < 4; ++e) {
-            // Horner over the weight groups.  fma is used ONLY here; on integers below 2^53 t*256 + acc is exact, so the
-            // fused and the two-step form give the same bits (the reference-order arithmetic below stays unfused).
-            double t = 0.0;
-            bool started = false;
-#pragma unroll
-            for (int g = DENSE_MAX_GROUPS - 1; g >= 0; --g)
-              if ((uint32_t)g < ngr) {
-                t = started ? __fma_rn(t, 256.0, (double)acc[g][4 * qd + e]) : (double)acc[g][4 * qd + e];
-                started = true;
-              }
+            double t = hsum[ci][4 * qd + e];
             if (!NGR && w0 != 1.0) t = __dmul_rn(t, w0);
             if (add_partial) t = __dadd_rn(t, part[(size_t)(c0 + 4 * qd + e) * 128]);
             sum[e] = t;
@@ -450,13 +475,15 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
           *reinterpret_cast<int4*>(gp) = o;
         }
       }
+#ifdef ECO_DENSE_LATE_RELEASE   // A/B build (tools/variants.sh): hold the accumulators until the update is stored, as round 1 did
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_tempty);
-      ex += clock64() - e1;
+#endif
+      ex += clock64() - e2;
       ++k;
     }
-    if (p.prof && warp == 2 && lane == 0) { p.prof[blockIdx.x * 8 + 4] = ew; p.prof[blockIdx.x * 8 + 5] = ex; }
+    if (p.prof && warp == 2 && lane == 0) { p.prof[blockIdx.x * 8 + 4] = ew; p.prof[blockIdx.x * 8 + 5] = ex; p.prof[blockIdx.x * 8 + 6] = ed; }
   }
 
   tc_fence_before();

@@ -695,6 +695,8 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "ny_local") *out = (double)m->nyl;
   else if (s == "panmictic") *out = m->panmictic ? 1.0 : 0.0;
   else if (s == "buf_version") *out = (double)m->eng.buf_version();
+  else if (s == "tile_width") *out = (double)m->eng.tile_width();     // cells per tile of the blocked layout (tests, tools)
+  else if (s == "capacity") *out = (double)m->eng.capacity();
   else if (s == "peer_connected") *out = m->eng.peer_connected() ? 1.0 : 0.0;
   else throw std::runtime_error("unknown scalar member: " + s);
   ECO_CATCH

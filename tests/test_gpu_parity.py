@@ -226,6 +226,45 @@ def test_condense_bit_exact(oracle_mod, gpu, grid, nsp, k):
     assert np.array_equal(gpu_density(m, grid), oracle_density(o, grid))
 
 
+@pytest.mark.parametrize("grid,nsp,ndead,tw_before,tw_after", [((24, 5), 600, 150, 16, 32), ((20, 3), 1900, 300, 8, 16),
+                                                               ((19, 2), 3650, 200, 4, 8)])
+def test_condense_retiles_to_the_wider_tile(oracle_mod, gpu, grid, nsp, ndead, tw_before, tw_after):
+    """The blocked layout follows the species count both ways: condense() below a tile-width threshold re-lays the
+    densities out on the wider tile, the next mutate() that outgrows the capacity goes back -- same bits throughout."""
+    ncells = grid[0] * grid[1]
+    O = oracle_mod
+    p = synth(nsp, 2, 12, mig=0.05, mut=400.0 / (ncells * nsp))     # ~100 mutants per mutate() and unit of time
+    d = densities(ncells, nsp, 12)
+    d[:, nsp - ndead:] = 0
+    d[:, 7] = 0
+    o = load_oracle(oracle_mod, p, d, grid, seed=12); m = load_gpu(gpu, p, d, grid, seed=12)
+    try:
+        assert int(m._scalar("tile_width")) == tw_before
+        o.generate(1); m.generate(1)
+        removed = o.condense()
+        assert m.condense() == removed and removed >= ndead
+        assert int(m._scalar("tile_width")) == tw_after and int(m._scalar("capacity")) >= nsp - removed
+        assert np.array_equal(m.density_array(), o.get_density_all())
+        for it in range(3):
+            o.generate(2); m.generate(2)
+            assert o.migrate() == m.migrate()
+            assert np.array_equal(m.density_array(), o.get_density_all())
+            assert np.array_equal(m.species_totals(), o.get_density_all().astype(np.int64).sum(axis=0))
+        nb = int(m._scalar("nsp"))
+        for it in range(4):                       # speciation until the capacity (and with it the tile width) changes again
+            o.generate(1); m.generate(1)
+            O.srand(300 + it); O.reset_grand(); o.mutate()
+            gpu.lib().eco_array_urand_seed(300 + it); gpu.lib().eco_array_grand_reset(); m.mutate()
+            assert int(m._scalar("nsp")) == o.nsp
+            assert np.array_equal(m.density_array(), o.get_density_all())
+        assert o.nsp > nb and int(m._scalar("tile_width")) <= tw_after and int(m._scalar("capacity")) >= o.nsp
+        o.generate(2); m.generate(2)
+        assert o.migrate() == m.migrate()
+        assert np.array_equal(m.density_array(), o.get_density_all())
+    finally:
+        m.close()
+
+
 def test_condense_sh(gpu):
     """test/00/condense.sh:14-21 through the reference-facing API."""
     m = gpu.PanmicticModel(0)
