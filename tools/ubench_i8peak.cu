@@ -1,6 +1,6 @@
 // ubench_i8peak.cu -- the tensor-core ceiling the dense generate kernel (ecolab_b200/csrc/k_dense.cuh) is measured against:
 // every SM issues back-to-back tcgen05.mma.cta_group::1.kind::i8 (M128 x N x K32 B, SWIZZLE_128B operands resident in
-// shared memory, no loads, no epilogue) for tens of milliseconds; reported per case: cycles per MMA, the SM clock the
+// shared memory, no loads, no epilogue) for ~0.15 s per pass; reported per case: cycles per MMA, the SM clock the
 // kernel really ran at (cycles / globaltimer ns -- the int8 pipe is power-capped), and the whole-GPU rate in TOP/s
 // (2 ops per MAC).  Operand bytes: random (the dense path's regime) or zero (no datapath toggling: shows what the power cap costs).
 // Development tool, not product.
