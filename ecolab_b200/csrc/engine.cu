@@ -102,7 +102,8 @@ Engine::~Engine() {
   try { peer_disconnect(); } catch (...) {}
   free_buffers();
   cudaFree(d_flags_);
-  cudaFree(d_boff_); cudaFree(d_stream_);
+  cudaFree(d_boff_); cudaFree(d_stream_); cudaFree(d_csr_);
+  if (h_csr_) cudaFreeHost(h_csr_);
   cudaFree(d_aop_); cudaFree(d_bop_); cudaFree(d_dsp_); cudaFree(d_partial_); cudaFree(d_maxn_); cudaFree(dense_prof_);
   if (h_maxn_) cudaFreeHost(h_maxn_);
   cudaFree(d_vec_); cudaFree(d_mask_); cudaFree(d_map_); cudaFree(d_total_); cudaFree(d_rec_); cudaFree(d_scan_); cudaFree(d_stage_); cudaFree(d_scratch_);

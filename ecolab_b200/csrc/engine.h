@@ -66,7 +66,7 @@ class Engine {
   void fill_density_random(uint32_t seed, int32_t lo, int32_t hi);   // lo + philox(stage 3) % (hi-lo+1)
 
   // ---- species data ---------------------------------------------------------
-  void upload_beta(const BetaCsr& b);
+  void upload_beta(BetaCsr b);
 
   // ---- hot path -------------------------------------------------------------
   // niter fused Lotka-Volterra steps on every owned cell; t0 = absolute tstep of the first
@@ -196,6 +196,7 @@ class Engine {
   uint32_t nblocks_ = 0, beta_tw_ = 0, beta_nsp_ = 0;   // ELL blocks; the tile width / species count it was built for
   uint32_t* d_boff_ = nullptr; void* d_stream_ = nullptr;   // blocked-ELL stream (k_generate.cuh)
   size_t beta_cap_slots_ = 0, beta_cap_blocks_ = 0, beta_slots_ = 0;
+  void* h_csr_ = nullptr; void* d_csr_ = nullptr; size_t csr_cap_ = 0;   // CSR staging (pinned) and its device copy, input of ell_build_kernel
   bool beta_fma_ok_ = true;    // every beta entry is zero or a normal number below 2^971: the exact-FMA product applies
   uint32_t beta_uslots_ = 0;   // != 0: every block of the stream has this many slots (uniform width, no offset table reads)
   BetaCsr beta_host_;                                   // kept to re-block when the tile width changes

@@ -346,6 +346,38 @@ __global__ void __launch_bounds__(1024) transpose_kernel(const Layout L, int32_t
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// beta: CSR -> the blocked-ELL record stream of k_generate.cuh.  Block k = slots [boff[k], boff[k+1]) of R 16-byte records:
+// slot 0 holds {diag, repro_rate} of the block's R species rows, slot 1 + e the e-th term of each row
+// {val, byte offset of the term's species row inside a tile, high word of c = -(val * 2^52)}; everything else is the padding
+// record {0.0, offset 0, -0.0} (a term that adds exactly nothing).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ell_build_kernel(const uint32_t* __restrict__ boff, uint32_t nblocks, uint32_t R, uint32_t nsp, uint32_t tw,
+                                                        const uint32_t* __restrict__ rowptr, const uint32_t* __restrict__ col,
+                                                        const double* __restrict__ val, const double* __restrict__ diag,
+                                                        const double* __restrict__ rr, uint4* __restrict__ stream) {
+  for (uint32_t k = blockIdx.x; k < nblocks; k += gridDim.x) {
+    const uint32_t s0 = boff[k], nrec = (boff[k + 1] - s0) * R;
+    for (uint32_t i = threadIdx.x; i < nrec; i += blockDim.x) {
+      const uint32_t slot = i / R, row = k * R + i % R;
+      uint4 rec = make_uint4(0u, 0u, 0u, 0x80000000u);
+      if (row < nsp) {
+        if (slot == 0) {
+          const double d = diag[row], q = rr[row];
+          rec = make_uint4((uint32_t)__double2loint(d), (uint32_t)__double2hiint(d), (uint32_t)__double2loint(q), (uint32_t)__double2hiint(q));
+        } else {
+          const uint32_t e = rowptr[row] + slot - 1u;
+          if (e < rowptr[row + 1]) {
+            const double v = val[e], c = -__dmul_rn(v, 4503599627370496.0);
+            rec = make_uint4((uint32_t)__double2loint(v), (uint32_t)__double2hiint(v), col[e] * tw * 4u, (uint32_t)__double2hiint(c));
+          }
+        }
+      }
+      stream[(size_t)s0 * R + i] = rec;
+    }
+  }
+}
+
 // copy every (row incl. ghosts, cell, species < nrows) from one blocked layout to another (different cap / tw);
 // the destination has been zero-filled
 __global__ void relayout_kernel(const Layout S, const Layout D, uint32_t nrows_y, uint32_t nrows_s) {

@@ -191,7 +191,7 @@ struct eco_model {
     }
     b.diag = diag;
     b.rr = repro_rate;
-    eng.upload_beta(b);
+    eng.upload_beta(std::move(b));
     beta_dirty = false;
   }
 
