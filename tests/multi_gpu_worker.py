@@ -22,10 +22,13 @@ def main():
     comm = E.Comm()
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)                 # kernels and NCCL on one stream: the configuration bench.py runs
-    nx, ny, nsp, k, seed = 37, 19, 45, 3, 7
+    nx, ny, nsp, k, seed = 37, 19, int(os.environ.get("ECO_MULTI_NSP", "45")), 3, 7
+    ndead = int(os.environ.get("ECO_MULTI_DEAD", "0"))
     p = synth(nsp, k, seed, mig=0.07, mut=2e-3)
     d = densities(nx * ny, nsp, seed)
     d[:, 4] = 0                                   # one species extinct everywhere -> condense removes it on every rank
+    if ndead:                                     # ... and enough of them to cross a tile-width threshold: every rank re-tiles
+        d[:, nsp - ndead:] = 0
     m = E.SpatialModel(local, comm)
     m.set_stream(stream)
     for kk, v in SCALARS.items():
@@ -69,10 +72,20 @@ def main():
         if rank == 0:
             assert moved == o.migrate(), f"migrate total {it}"
         check(f"migrate {it}")
+    tw0 = int(m._scalar("tile_width"))
     removed = m.condense()
     if rank == 0:
-        assert removed == o.condense() and removed >= 1
+        assert removed == o.condense() and removed >= 1 + ndead
     check("condense")
+    if ndead:                                     # the layout changed under the peer-memory halo: it has to reconnect
+        assert int(m._scalar("tile_width")) > tw0, "condense must have re-tiled"
+        m.generate(1)
+        if rank == 0:
+            o.generate(1)
+        moved = m.migrate()
+        if rank == 0:
+            assert moved == o.migrate(), "migrate total after the re-tiling"
+        check("migrate after the re-tiling")
     # mutate: the cell-side speciation is deterministic (Philox); the parameter draws come from rank 0's libc stream
     # (ModelData::mutate runs on rank 0 only, :251-258), seeded here exactly like the oracle's -> everything must be equal
     before = int(gathered().sum())

@@ -35,3 +35,20 @@ def test_partitioned_model_matches_oracle(world, halo):
         if "EADDRINUSE" not in r.stderr:
             break
     assert r.returncode == 0 and f"MULTI_GPU_OK {world} {halo}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("halo", ["peer", "nccl"])
+def test_partitioned_model_retiles_on_every_rank(halo):
+    """560 species of which 61 are extinct: condense() crosses the 512-row threshold, every rank re-lays its slab out on
+    32-cell tiles (same decision everywhere), the halo reconnects to the new buffers, and the run stays the oracle's."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, ECOLAB_B200_HALO=halo, ECO_MULTI_NSP="560", ECO_MULTI_DEAD="60")
+    for attempt in range(3):
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+               "--master-port", str(_port()), os.path.join(HERE, "multi_gpu_worker.py")]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+        if "EADDRINUSE" not in r.stderr:
+            break
+    assert r.returncode == 0 and f"MULTI_GPU_OK 2 {halo}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
