@@ -94,6 +94,7 @@ _SPECIAL = {
     "eco_last_error": (_cp, []),
     "eco_version": (_cp, []),
     "eco_array_urand_seed": (None, [_int]),
+    "eco_array_urand_rand": (None, [_vp, _sz]),
     "eco_array_grand_reset": (None, []),
 }
 

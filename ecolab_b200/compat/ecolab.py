@@ -12,7 +12,12 @@ class _Urand:
         lib().eco_array_urand_seed(int(s))
 
     def rand(self):
-        raise NotImplementedError("array_urand.rand() is only used inside the model")
+        """urand::rand (src/random.cc:57): the next rand()/RAND_MAX of the stream the model's parameter mutation draws from."""
+        import ctypes
+        from ecolab_b200 import lib
+        v = ctypes.c_double()
+        lib().eco_array_urand_rand(ctypes.byref(v), 1)
+        return v.value
 
 
 class _Grand:

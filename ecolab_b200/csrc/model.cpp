@@ -1170,6 +1170,7 @@ int eco_append_species(eco_model* m, const uint32_t* cells, size_t n) {
 }
 
 void eco_array_urand_seed(int seed) { g_urand.seed((unsigned)seed); }
+void eco_array_urand_rand(double* out, size_t n) { for (size_t k = 0; k < n; ++k) out[k] = urand01(); }
 void eco_array_grand_reset(void) { g_grand = RunningClt(); }
 
 int eco_set_tuning(eco_model* m, const char* knob, int value) {

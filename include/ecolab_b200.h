@@ -200,6 +200,8 @@ int eco_append_species(eco_model* m, const uint32_t* birth_cells, size_t n);
  * array_urand.seed (include/random_basic.h:15: srand) and the process-wide
  * array_grand running-CLT generator (src/random.cc:59-64, src/arrays.cc:24-25). */
 void eco_array_urand_seed(int seed);
+/* array_urand.rand(): n values of rand()/RAND_MAX from the same stream (src/random.cc:57, include/random_basic.h:14) */
+void eco_array_urand_rand(double* out, size_t n);
 void eco_array_grand_reset(void);
 
 /* tuning / profiling knobs (0 = automatic): "gen_dual" (-1: one species-row block per consumer warp of generate(1)),

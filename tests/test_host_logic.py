@@ -103,3 +103,38 @@ def test_distributed_driver_gloo_world2():
         p.join(10)
     for r, msg in res:
         assert msg == "ok", f"rank {r}: {msg}"
+
+
+def test_array_urand_is_libc_rand():
+    """array_urand (src/random.cc:57: rand()/RAND_MAX) is restated inside the library so that the model owns the state: it
+    must be libc's own rand() stream, however the draws are grouped."""
+    import ctypes
+    import numpy as np
+    from ecolab_b200 import _cabi
+    if not os.path.exists(_cabi.LIB_PATH):
+        pytest.skip("library not built")
+    L = ctypes.CDLL(_cabi.LIB_PATH)          # no device needed: the generator is host state
+    L.eco_array_urand_seed.argtypes = [ctypes.c_int]; L.eco_array_urand_seed.restype = None
+    L.eco_array_urand_rand.argtypes = [ctypes.c_void_p, ctypes.c_size_t]; L.eco_array_urand_rand.restype = None
+    libc = ctypes.CDLL("libc.so.6")
+    libc.rand.restype = ctypes.c_int
+
+    def draw(n):
+        a = np.empty(n, dtype=np.float64)
+        L.eco_array_urand_rand(a.ctypes.data_as(ctypes.c_void_p), n)
+        return a
+
+    for seed in (1, 10, 12345):
+        libc.srand(seed)
+        want = np.array([libc.rand() for _ in range(5000)], dtype=np.float64) / 2147483647.0
+        L.eco_array_urand_seed(seed)
+        one = np.concatenate([draw(1) for _ in range(5000)])
+        assert np.array_equal(one, want)
+        L.eco_array_urand_seed(seed)
+        assert np.array_equal(draw(5000), want)                      # one block
+        L.eco_array_urand_seed(seed)
+        sizes, got = [1, 8, 3, 191, 192, 193, 2, 577, 31, 64, 7, 1000, 9, 5], []
+        for n in sizes:                                              # singles and blocks interleaved: the state carries over
+            got.append(draw(n))
+        got = np.concatenate(got)
+        assert np.array_equal(got, want[:len(got)])
