@@ -519,7 +519,10 @@ def dense_leg(E, args, local, stream, steps, warmup, sparse_too=False):
         m.set_tuning("dense_slices", args.dense_slices)
     m.fill_density_random(0, args.dense_dmax)   # < 256: one u8 slice per density; larger: two
     updates = nx * ny * nsp
-    m._scalar("dense_prof0")         # enables the in-kernel cycle counters (computed anyway; this only stores them)
+    if args.dense_prof:
+        m._scalar("dense_prof0")     # per-stage cycle counters of the issuing thread (tools: they slow it down)
+    else:
+        m._scalar("dense_clock_mhz")   # two clock reads per launch: the SM clock the kernel really runs at
     for _ in range(warmup):
         m.step(1, wait=False)
     assert m._scalar("dense_active") == 1
@@ -555,24 +558,26 @@ def dense_leg(E, args, local, stream, steps, warmup, sparse_too=False):
                 "beta_slices": int(args.dense_slices or 3), "density_slices": q,
                 "kernels_ms_per_step": {k: v[0] / steps for k, v in kt.items() if v[1]}}
     # the int8 ceiling measured with tools/ubench_i8peak.cu (bare kind::i8 MMAs from resident random operands, all SMs, under
-    # the part's power cap) and the shared-memory fill bound of DESIGN.md 5a: (P + Q) x 16 KB of bulk copies per 128-byte K step
-    # against the measured 68 B/clk/SM L2 -> shared ceiling (profiles/r1_ubench_tma.txt)
+    # the part's power cap), and the bound that actually holds the kernel: shared-memory bandwidth.  Per 128-byte
+    # K chunk of a tile the bulk copies WRITE (P + Q) x 16 KB into shared memory and the MMAs READ their operands from it -- an
+    # M128 x N x 32 B MMA reads 4 KB of beta and N/128 x 4 KB of densities -- at 128 B/clk/SM for both together.
     ipk = os.path.join(ROOT, "profiles", "int8_peak.json")
     if os.path.exists(ipk):
         ip = json.load(open(ipk))
         roofline["int8_peak_tops"] = ip["tops_random_operands_n128"]
         roofline["int8_frac"] = achieved / ip["tops_random_operands_n128"]
         roofline["int8_peak_source"] = ip["source"]
-        # the SM clock inside the kernel: CTA 0's cycle counters over the globaltimer span of its issue loop (the kernel runs
-        # under sw_power_cap; nvidia-smi's samples also see the gaps between launches)
-        prof = [m._scalar(f"dense_prof{i}") for i in range(8)]
-        mhz = (prof[0] + prof[1] + prof[2]) / prof[7] * 1e3 if prof[7] else clocks.get("sm_mhz")
+        mhz = m._scalar("dense_clock_mhz") or clocks.get("sm_mhz")
         if mhz and q:
-            slices_b = int(args.dense_slices or 3) + q
-            fill_ms = (macs / (int(args.dense_slices or 3) * q) / (128.0 * 128 * 128)) * slices_b * 16384 / (
-                ip["l2_to_shared_bytes_per_clk_per_sm"] * 148 * mhz * 1e3)
-            roofline["fill_bound"] = {"stage_bytes": slices_b * 16384, "ceiling_bytes_per_clk_per_sm": ip["l2_to_shared_bytes_per_clk_per_sm"],
-                                      "sm_mhz_in_kernel": mhz, "floor_ms": fill_ms, "frac": fill_ms / (mma_ms * launches_per_step)}
+            P = int(args.dense_slices or 3)
+            stages = macs / (P * q) / (128.0 * 128 * 128)                      # (tile, K chunk) pairs of one step, all SMs
+            reads = 4 * P * (4096 + q * 4096) if q <= 2 else 4 * P * q * 8192   # q <= 2: the density slices ride one N = 128q MMA
+            writes = (P + q) * 16384
+            floor_ms = stages * (reads + writes) / (ip["shared_memory_bytes_per_clk_per_sm"] * 148 * mhz * 1e3)
+            roofline["shared_memory_bound"] = {"bytes_per_stage": {"operand_reads": reads, "bulk_copy_writes": writes},
+                                               "bytes_per_clk_per_sm": ip["shared_memory_bytes_per_clk_per_sm"], "sm_mhz_in_kernel": mhz,
+                                               "floor_ms": floor_ms, "frac": floor_ms / (mma_ms * launches_per_step),
+                                               "tensor_pipe_ceiling_in_this_tile_shape": 4 * P * (64 if q == 1 else 128 if q == 2 else 64 * q) * 128.0 / (reads + writes)}
     sparse_ms = None
     if sparse_too:   # the FP64 sparse kernel on the same dense model (config 5: "tcgen05 contraction path vs sparse path")
         try:

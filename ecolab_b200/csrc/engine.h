@@ -154,7 +154,9 @@ class Engine {
   int gen_dense = 0;
   int dense_slices = 3;
   bool dense_wanted() const;
-  void dense_profile(unsigned long long* out8);   // enables the in-kernel cycle counters; returns CTA 0's of the last launch
+  // CTA 0's counters of the last dense launch; the first call switches them on: [2] cycles and [7] ns of the issue loop always,
+  // the per-stage split ([0] wait TMEM, [1] wait stage, [2] issue, [4..6] epilogue) only with detail (it slows the issuing thread)
+  void dense_profile(unsigned long long* out8, bool detail);
   uint32_t dense_last_q() const { return dense_q_; }        // density slices used by the last dense generate
   uint64_t dense_mma_per_step() const { return dense_macs_; }   // integer MACs issued by the last dense generate step
 
@@ -209,7 +211,7 @@ class Engine {
   unsigned int* d_maxn_ = nullptr; unsigned int* h_maxn_ = nullptr;
   uint32_t dense_p_ = 0, dense_nsp_ = 0, dense_mtiles_ = 0, dense_nkc_ = 0, dense_q_ = 1;
   uint64_t dense_macs_ = 0;
-  unsigned long long* dense_prof_ = nullptr;
+  unsigned long long* dense_prof_ = nullptr; bool dense_prof_detail_ = false;
   uint64_t beta_version_ = 0, dense_version_ = ~0ull;
 
   // scratch

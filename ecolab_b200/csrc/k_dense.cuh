@@ -60,7 +60,7 @@ struct DenseParams {
   uint32_t P, Q;               // slices of beta / of the densities
   uint32_t g0, g1;             // groups [g0, g1) handled by this launch (g1 - g0 <= 4)
   double w0;                   // 256^g0, the weight of the lowest group of this launch
-  uint32_t flags;              // 1: add `partial` to this round's sum   2: store the sum to `partial`, no epilogue
+  uint32_t flags;              // 1: add `partial` to this round's sum   2: store the sum to `partial`, no epilogue   4: per-stage cycle counters
   uint32_t nkc, mtiles, ntn;   // K chunks, 128-row species tiles, 128-column cell tiles
   uint32_t mblock;             // species tiles per L2 super-block (tile order: [m block][n tile][m in block])
   uint32_t nxq;                // padded quads per grid row = ntx*TW/4
@@ -109,13 +109,14 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int (&v)[8]) {
 // returns at once, the kernel runs out, and the host finds the word at its next synchronisation and throws.
 __device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity, unsigned int* err) {
   uint32_t done = 0;
-  const long long t0 = clock64();
+  long long t0 = 0;
   for (uint32_t spin = 0;; ++spin) {
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(done)
                  : "r"(smem_u32(bar)), "r"(parity)
                  : "memory");
     if (done) return;
+    if (spin == 0) t0 = clock64();   // the clock is read only once a wait really waits (the MMA thread's common case does not)
     if ((spin & 1023u) == 1023u) {
       if (*reinterpret_cast<volatile unsigned int*>(err)) return;
       if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); return; }   // ~10 s without progress
@@ -283,6 +284,10 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
     // ===================== MMA issuer =====================
     if (lane == 0) {
       long long pc[3] = {0, 0, 0};
+      // per-stage cycle counters cost the ONE issuing thread three clock reads per stage: only on request (flags & 4, tools);
+      // otherwise prof[2] is the cycle count of the whole loop, which with prof[7] (its wall time) gives the kernel's real SM clock
+      const bool prof = p.prof != nullptr && (p.flags & 4u);
+      const long long cstart = p.prof ? clock64() : 0;
       unsigned long long ns0 = 0;
       if (p.prof) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns0));
       // compile-time issue paths: single-round launches of the common slicings, and the two rounds of P = 3 with Q = 3 / 4
@@ -292,17 +297,17 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
       for (uint32_t id = blockIdx.x; id < ntile_ids; id += gridDim.x) {
         uint32_t mt, nt;
         if (!dense_tile(p, id, mt, nt)) continue;
-        long long c0 = clock64();
+        long long c0 = prof ? clock64() : 0;
         if (k) mbar_wait_wd(&s_tempty, (k - 1u) & 1u, p.err);   // the epilogue has drained the accumulators of the previous tile
         tc_fence_after();
-        pc[0] += clock64() - c0;
+        if (prof) pc[0] += clock64() - c0;
         uint32_t written = 0;                             // groups that already hold a partial sum of this tile
         for (uint32_t kc = 0; kc < p.nkc; ++kc) {
-          c0 = clock64();
+          if (prof) c0 = clock64();
           mbar_wait_wd(s_full + stage, round & 1u, p.err);
           tc_fence_after();
-          const long long c1 = clock64();
-          pc[1] += c1 - c0;
+          const long long c1 = prof ? clock64() : 0;
+          if (prof) pc[1] += c1 - c0;
           const uint32_t sa = smem_u32(dense_smem + (size_t)stage * stage_bytes);
           const uint32_t a_lo = (sa >> 4) | (1u << 16), b_lo = ((sa + a_bytes) >> 4) | (1u << 16);
           if (fast == 31u) { if (kc) dense_issue_stage<3, 1, false>(tmem, a_lo, b_lo); else dense_issue_stage<3, 1, true>(tmem, a_lo, b_lo); }
@@ -328,12 +333,13 @@ __global__ void __launch_bounds__(DENSE_THREADS, 1) generate_dense_kernel(const 
                 }
           }
           umma_commit(s_empty + stage);                   // stage reusable once these MMAs have read it
-          pc[2] += clock64() - c1;
+          if (prof) pc[2] += clock64() - c1;
           if (++stage == S) { stage = 0; ++round; }
         }
         umma_commit(&s_tfull);                            // accumulators complete
         ++k;
       }
+      if (p.prof && !prof) pc[2] = clock64() - cstart;
       if (p.prof) { p.prof[blockIdx.x * 8 + 0] = pc[0]; p.prof[blockIdx.x * 8 + 1] = pc[1]; p.prof[blockIdx.x * 8 + 2] = pc[2]; p.prof[blockIdx.x * 8 + 3] = k;
         unsigned long long ns1;   // wall time of the issue loop: cycles / ns = the SM clock the kernel really ran at
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));

@@ -687,8 +687,13 @@ int eco_get_scalar(eco_model* m, const char* name, double* out) {
   else if (s == "dense_macs") *out = (double)m->eng.dense_mma_per_step();
   else if (s.rfind("dense_prof", 0) == 0) {   // dense_prof0..7: in-kernel cycle counters of CTA 0 (first call enables them)
     unsigned long long v[8];
-    m->eng.dense_profile(v);
+    m->eng.dense_profile(v, true);
     *out = (double)v[std::min(7, std::max(0, s.size() > 10 ? s[10] - '0' : 0))];
+  }
+  else if (s == "dense_clock_mhz") {   // SM clock inside the last dense launch: cycles / ns of CTA 0's issue loop (first call enables it)
+    unsigned long long v[8];
+    m->eng.dense_profile(v, false);
+    *out = v[7] ? (double)(v[0] + v[1] + v[2]) / (double)v[7] * 1e3 : 0.0;
   }
   else if (s == "nprocs") *out = (double)m->nprocs;
   else if (s == "y0") *out = (double)m->y0;
