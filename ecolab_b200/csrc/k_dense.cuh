@@ -30,8 +30,12 @@
 //   warp 0 : producer   -- bulk copies of stage (tile, kc) into a ring, "full"/"empty" mbarriers
 //   warp 1 : MMA issuer -- one lane issues P*Q*(KC/32) tcgen05.mma per stage into <= 4 accumulators of 128 columns,
 //                          tcgen05.commit frees the stage / publishes the accumulators
-//   warps 2..17 : epilogue -- tcgen05.ld (lane = species row, 32 columns per warp), Horner, generate arithmetic,
-//                            Philox ROUND, STG.128; the densities of the next 8 columns are prefetched meanwhile
+//   warps 2..17 : epilogue -- tcgen05.ld of the warp's 32 columns of every group (lane = species row), Horner into FP64 sums
+//                            held in registers, accumulators handed back to the MMA warp at once; then the generate
+//                            arithmetic, Philox ROUND and STG.128 run beside the next tile's MMAs (the densities of the next
+//                            8 columns are prefetched meanwhile)
+// Bound: shared-memory bandwidth -- per K chunk the bulk copies write (P + Q) x 16 KB and the MMAs read
+// 4 KB of beta + N/128 x 4 KB of densities each, 160 KB per stage at P = 3, Q = 1 through 128 B/clk = 1250 cycles (768 tensor).
 #pragma once
 #include "k_common.cuh"
 #include "k_generate.cuh"
