@@ -364,6 +364,8 @@ struct eco_model {
     if (!m) return;
     const size_t n0 = nsp();
     for (uint32_t p : parents) if (p >= n0) throw std::runtime_error("mutate: parent slot out of range");
+    for (size_t j = 0; j < row.size(); ++j)   // before anything is modified
+      if (row[j] >= n0 || col[j] >= n0) throw std::runtime_error("mutate: interaction.row/col index out of range");
     if (sp_cntr == -1) sp_cntr = *std::max_element(species.begin(), species.end()) + 1;
 
     std::vector<double> gd(m);                                   // genetic distances (:371-373)
@@ -400,18 +402,36 @@ struct eco_model {
     // The reference's dense temporaries of nsp+i elements per mutant are kept (the gaussians are drawn per ELEMENT), but
     // everything after the draws walks only the elements that can be non-zero: the ascending union of the two index lists
     // perturb_links returns -- the same elements, in the same order, as the reference's dense loops meet them.
-    std::vector<std::vector<uint32_t>> byrow(n0 + m), bycol(n0 + m);
-    for (size_t j = 0; j < row.size(); ++j) { byrow[row[j]].push_back((uint32_t)j); bycol[col[j]].push_back((uint32_t)j); }
+    // The lists of the existing entries are two counting sorts into flat arrays (stable: ascending j inside a row / column);
+    // entries appended during this batch go to small per-species lists behind them -- only parents (< n0) are ever looked up.
+    const size_t nnz0 = row.size();
+    std::vector<uint32_t> rstart(n0 + 1, 0), cstart(n0 + 1, 0), ridx(nnz0), cidx(nnz0);
+    for (size_t j = 0; j < nnz0; ++j) { ++rstart[row[j] + 1]; ++cstart[col[j] + 1]; }
+    for (size_t i = 0; i < n0; ++i) { rstart[i + 1] += rstart[i]; cstart[i + 1] += cstart[i]; }
+    {
+      std::vector<uint32_t> rp(rstart.begin(), rstart.end() - 1), cp(cstart.begin(), cstart.end() - 1);
+      for (size_t j = 0; j < nnz0; ++j) { ridx[rp[row[j]]++] = (uint32_t)j; cidx[cp[col[j]]++] = (uint32_t)j; }
+    }
+    std::vector<std::vector<uint32_t>> xrow(n0), xcol(n0);
+    // f(j) for every entry j of row / column p, in COO order
+    auto each_in_row = [&](uint32_t p, auto&& f) {
+      for (uint32_t k = rstart[p]; k < rstart[p + 1]; ++k) f(ridx[k]);
+      for (uint32_t j : xrow[p]) f(j);
+    };
+    auto each_in_col = [&](uint32_t p, auto&& f) {
+      for (uint32_t k = cstart[p]; k < cstart[p + 1]; ++k) f(cidx[k]);
+      for (uint32_t j : xcol[p]) f(j);
+    };
     std::vector<double> rw(n0 + m, 0.0), cl(n0 + m, 0.0);
     std::vector<uint32_t> nzr, nzc, both;
     for (size_t i = 0; i < m; ++i) {
       const size_t L = n0 + i;   // index of the new species; length of the dense temporaries (:411)
       const uint32_t p = parents[i];
       nzr.clear(); nzc.clear(); both.clear();
-      for (uint32_t j : byrow[p]) if (col[j] < L) rw[col[j]] = val[j];
+      each_in_row(p, [&](uint32_t j) { if (col[j] < L) rw[col[j]] = val[j]; });
       rw[p] = diag[p];
       perturb_links(rw, L, range, odiag_min, gd[i], nzr);
-      for (uint32_t j : bycol[p]) if (row[j] < L) cl[row[j]] = val[j];
+      each_in_col(p, [&](uint32_t j) { if (row[j] < L) cl[row[j]] = val[j]; });
       cl[p] = diag[p];
       perturb_links(cl, L, range, odiag_min, gd[i], nzc);
       std::set_union(nzr.begin(), nzr.end(), nzc.begin(), nzc.end(), std::back_inserter(both));
@@ -435,17 +455,17 @@ struct eco_model {
       }
       for (uint32_t q : nzr)
         if (rw[q] != 0.0) {
-          byrow[L].push_back((uint32_t)val.size()); bycol[q].push_back((uint32_t)val.size());
+          if (q < n0) xcol[q].push_back((uint32_t)val.size());     // entry (L, q): a new element of column q
           val.push_back(rw[q]); row.push_back((uint32_t)L); col.push_back((uint32_t)q);
         }
       for (uint32_t q : nzc)
         if (cl[q] != 0.0) {
-          byrow[q].push_back((uint32_t)val.size()); bycol[L].push_back((uint32_t)val.size());
+          if (q < n0) xrow[q].push_back((uint32_t)val.size());     // entry (q, L): a new element of row q
           val.push_back(cl[q]); row.push_back((uint32_t)q); col.push_back((uint32_t)L);
         }
       // back to all-zero for the next mutant: everything that was written is in the scatter lists or in nzr / nzc
-      for (uint32_t j : byrow[p]) if (col[j] < rw.size()) rw[col[j]] = 0.0;
-      for (uint32_t j : bycol[p]) if (row[j] < cl.size()) cl[row[j]] = 0.0;
+      each_in_row(p, [&](uint32_t j) { if (col[j] < rw.size()) rw[col[j]] = 0.0; });
+      each_in_col(p, [&](uint32_t j) { if (row[j] < cl.size()) cl[row[j]] = 0.0; });
       rw[p] = 0.0; cl[p] = 0.0;
       for (uint32_t q : nzr) rw[q] = 0.0;
       for (uint32_t q : nzc) cl[q] = 0.0;
